@@ -1,0 +1,234 @@
+// b2_attention.cu — masked self-attention for the encoder, head dim 64, on tcgen05 + TMA.
+//
+// One CTA handles one (sequence, head, 128-query block). For each 128-key block it runs
+//   S = Q·Kᵀ            tcgen05.mma 128x128x64   (Q, K: K-major 128-byte-swizzled TMA tiles)
+//   P = exp2((S-m)·c)    one thread per query row, S read from TMEM, keys >= len masked out
+//   O_blk = P·V          tcgen05.mma 128x64x128   (P: written to swizzled smem as the A operand,
+//                                                  V: MN-major TMA tile, no transpose needed)
+// and folds O_blk into a running, rescaled f32 accumulator held in registers (online softmax), so
+// S = 128 is one pass and S = 512 is four. Key blocks that lie wholly beyond the sequence's length
+// are never loaded.
+//
+// No reference counterpart: the reference's model is an opaque TFLite graph
+// (ops/map_classify_tpu.py:71-72). Semantics follow BertSelfAttention (scores/sqrt(d) + additive
+// key mask, softmax in f32, context = probs·V).
+#include "b2_kernels.h"
+
+namespace b2 {
+
+namespace {
+
+constexpr int ATT_THREADS = 160;  // warps 0-3: one query row per thread; warp 4: TMA + MMA issue
+constexpr int QB = 128;           // queries per CTA
+constexpr int KB = 128;           // keys per block
+constexpr int HD = 64;            // head dim
+constexpr uint32_t TILE_BYTES = 128 * 64 * 2;  // 16 KiB: a [128 x 64] bf16 tile
+constexpr uint32_t ATT_SMEM = 1024 + 3 * TILE_BYTES + 2 * TILE_BYTES + 64;
+
+__global__ void __launch_bounds__(ATT_THREADS, 2)
+attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out,
+                 const int32_t* __restrict__ lens, int S, int hidden, int heads, int qblocks) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t sQ = base;
+  const uint32_t sK = base + TILE_BYTES;
+  const uint32_t sV = base + 2 * TILE_BYTES;
+  const uint32_t sP = base + 3 * TILE_BYTES;  // two [128 x 64] K-major tiles (keys 0-63, 64-127)
+  const uint32_t bars = base + 5 * TILE_BYTES;
+  const uint32_t q_full = bars, kv_full = bars + 8, s_full = bars + 16, p_full = bars + 24,
+                 o_full = bars + 32, tmem_slot = bars + 40;
+  uint8_t* smem_aligned = smem_raw + (base - raw);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  int cta = blockIdx.x;
+  const int qb = cta % qblocks; cta /= qblocks;
+  const int h = cta % heads;
+  const int b = cta / heads;
+  int len = lens[b];
+  len = len < 0 ? 0 : (len > S ? S : len);
+  const int nkb = (len + KB - 1) / KB;
+  const int row0 = b * S;  // first token row of this sequence
+
+  if (threadIdx.x == 128) {
+    tma_prefetch_desc(&tmap_qkv);
+    mbar_init(q_full, 1);
+    mbar_init(kv_full, 1);
+    mbar_init(s_full, 1);
+    mbar_init(p_full, 128);
+    mbar_init(o_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 4) tmem_alloc<256>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t tmem_S = tmem_base;        // 128 columns
+  const uint32_t tmem_O = tmem_base + 128;  // 64 columns
+
+  if (warp == 4) {
+    if (lane == 0 && nkb > 0) {
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
+      mbar_expect_tx(q_full, TILE_BYTES);
+      tma_load_2d(sQ, &tmap_qkv, q_full, h * HD, row0 + qb * QB);
+      for (int kb = 0; kb < nkb; ++kb) {
+        if (kb > 0) mbar_wait(o_full, (kb - 1) & 1);  // P·V of the previous block has read K/V/P
+        mbar_expect_tx(kv_full, 2 * TILE_BYTES);
+        tma_load_2d(sK, &tmap_qkv, kv_full, hidden + h * HD, row0 + kb * KB);
+        tma_load_2d(sV, &tmap_qkv, kv_full, 2 * hidden + h * HD, row0 + kb * KB);
+        if (kb == 0) mbar_wait(q_full, 0);
+        mbar_wait(kv_full, kb & 1);
+        tc_fence_after();
+        {
+          const uint64_t qd = umma_desc_sw128(sQ, 16, 1024);
+          const uint64_t kd = umma_desc_sw128(sK, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) umma_bf16(tmem_S, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
+        }
+        umma_commit(s_full);
+        mbar_wait(p_full, kb & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < KB / 16; ++k) {
+          // A = P: K-major, 64 keys per 16 KiB tile, 32 bytes per K=16 step inside the swizzle atom
+          const uint64_t pd = umma_desc_sw128(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
+          // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes per step
+          const uint64_t vd = umma_desc_sw128(sV + k * 2048, 8192, 1024);
+          umma_bf16(tmem_O, pd, vd, idesc_o, k != 0);
+        }
+        umma_commit(o_full);
+      }
+    }
+  } else {
+    // ===== softmax / output rows: thread r owns query row r =====
+    const int r = threadIdx.x;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
+    float m_run = -INFINITY, l_run = 0.f;
+    float o[HD];
+#pragma unroll
+    for (int i = 0; i < HD; ++i) o[i] = 0.f;
+
+    for (int kb = 0; kb < nkb; ++kb) {
+      mbar_wait(s_full, kb & 1);
+      tc_fence_after();
+      const int kvalid = min(KB, len - kb * KB);
+      float mx = -INFINITY;
+      for (int c = 0; c < 4; ++c) {
+        if (c * 32 < kvalid) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_S + lane_base + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c * 32 + j < kvalid) mx = fmaxf(mx, __uint_as_float(v[j]));
+        }
+      }
+      const float m_new = fmaxf(m_run, mx);
+      const float alpha = exp2f((m_run - m_new) * sl2);
+      float rowsum = 0.f;
+      for (int c = 0; c < 4; ++c) {
+        uint32_t packed[16];
+        if (c * 32 < kvalid) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_S + lane_base + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            float p0 = (c * 32 + j < kvalid) ? exp2f((__uint_as_float(v[j]) - m_new) * sl2) : 0.f;
+            float p1 = (c * 32 + j + 1 < kvalid) ? exp2f((__uint_as_float(v[j + 1]) - m_new) * sl2) : 0.f;
+            rowsum += p0 + p1;
+            packed[j >> 1] = pack_bf16x2(p0, p1);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) packed[j] = 0u;
+        }
+        // keys [c*32, c*32+32) -> tile (c >> 1), 16-byte chunks ((c & 1) * 4 + j) ^ (r & 7)
+        uint8_t* tile = smem_aligned + 3 * TILE_BYTES + (c >> 1) * TILE_BYTES + r * 128;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
+          *reinterpret_cast<uint4*>(tile + chunk * 16) =
+              make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
+        }
+      }
+      l_run = l_run * alpha + rowsum;
+      m_run = m_new;
+      fence_proxy_async_smem();  // P was written through the generic proxy; the MMA reads it async
+      tc_fence_before();
+      mbar_arrive(p_full);
+
+      mbar_wait(o_full, kb & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_O + lane_base + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[c * 32 + j] = o[c * 32 + j] * alpha + __uint_as_float(v[j]);
+      }
+    }
+    const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+    __nv_bfloat16* dst = out + static_cast<size_t>(row0 + qb * QB + r) * hidden + h * HD;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      uint4 w;
+      w.x = pack_bf16x2(o[j * 8 + 0] * inv, o[j * 8 + 1] * inv);
+      w.y = pack_bf16x2(o[j * 8 + 2] * inv, o[j * 8 + 3] * inv);
+      w.z = pack_bf16x2(o[j * 8 + 4] * inv, o[j * 8 + 5] * inv);
+      w.w = pack_bf16x2(o[j * 8 + 6] * inv, o[j * 8 + 7] * inv);
+      *reinterpret_cast<uint4*>(dst + j * 8) = w;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem_base);
+  }
+}
+
+}  // namespace
+
+int attention_tmap_qkv(CUtensorMap* out, const void* qkv, int rows, int hidden) {
+  return make_tmap_bf16_2d(out, qkv, rows, 3 * hidden, static_cast<uint64_t>(3 * hidden) * 2, 128,
+                           64);
+}
+
+int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* out,
+                   const int32_t* lens, int B, int S, int hidden) {
+  if (B <= 0 || S <= 0 || (S % QB) != 0 || hidden <= 0 || (hidden % HD) != 0) {
+    set_last_error("attention_bf16: needs S %% 128 == 0 and hidden %% 64 == 0 (got S=%d hidden=%d)", S,
+                   hidden);
+    return B2_ERR_ARG;
+  }
+  static bool configured[64] = {};
+  int dev = 0;
+  B2_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 64 && !configured[dev]) {
+    B2_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    ATT_SMEM));
+    configured[dev] = true;
+  }
+  const int heads = hidden / HD, qblocks = S / QB;
+  const long long grid = 1ll * B * heads * qblocks;
+  if (grid > 0x7fffffffll) {
+    set_last_error("attention_bf16: grid too large");
+    return B2_ERR_ARG;
+  }
+  attention_kernel<<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM, stream>>>(
+      tqkv, out, lens, S, hidden, heads, qblocks);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+}  // namespace b2
