@@ -1,0 +1,250 @@
+// b2_rows.cu — the HBM-bound row kernels around the GEMMs: embedding gather + LayerNorm,
+// LayerNorm, the classifier head (logits, softmax, top-k, argmax, label histogram).
+//
+// Reference counterparts: the head replaces `_topk` (ops/map_classify_tpu.py:15-19: clamp k to
+// [1,n], descending by score) and the float32 read-back at ops/map_classify_tpu.py:74; embedding
+// and LayerNorm have none (BertEmbeddings / BertSelfOutput / BertOutput semantics, eps inside sqrt).
+//
+// One warp per row everywhere: 16- or 8-byte vector loads, f32 math, shuffle reductions.
+#include "b2_kernels.h"
+
+namespace b2 {
+
+namespace {
+
+constexpr int MAX_VEC = 8;  // hidden <= 8 * 128
+
+// ---- embedding gather + LayerNorm -------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+embed_ln_kernel(const int32_t* __restrict__ ids, const float* __restrict__ word,
+                const float* __restrict__ pos, const float* __restrict__ type0,
+                const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                __nv_bfloat16* __restrict__ out, int rows, int S, int hidden, int vocab) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  int id = ids[row];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const float* w = word + static_cast<size_t>(id) * hidden;
+  const float* p = pos + static_cast<size_t>(row % S) * hidden;
+  const int nvec = hidden >> 7;
+  float4 v[MAX_VEC];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    if (i < nvec) {
+      const int c = i * 128 + lane * 4;
+      const float4 a = __ldg(reinterpret_cast<const float4*>(w + c));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p + c));
+      const float4 t = __ldg(reinterpret_cast<const float4*>(type0 + c));
+      v[i] = make_float4(a.x + b.x + t.x, a.y + b.y + t.y, a.z + b.z + t.z, a.w + b.w + t.w);
+      sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
+  }
+  const float mean = warp_sum(sum) / hidden;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    if (i < nvec) {
+      const float dx = v[i].x - mean, dy = v[i].y - mean, dz = v[i].z - mean, dw = v[i].w - mean;
+      sq += (dx * dx + dy * dy) + (dz * dz + dw * dw);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / hidden + eps);
+  __nv_bfloat16* o = out + static_cast<size_t>(row) * hidden;
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    if (i < nvec) {
+      const int c = i * 128 + lane * 4;
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
+      const float4 bb = __ldg(reinterpret_cast<const float4*>(beta + c));
+      uint2 w2;
+      w2.x = pack_bf16x2((v[i].x - mean) * rstd * g.x + bb.x, (v[i].y - mean) * rstd * g.y + bb.y);
+      w2.y = pack_bf16x2((v[i].z - mean) * rstd * g.z + bb.z, (v[i].w - mean) * rstd * g.w + bb.w);
+      *reinterpret_cast<uint2*>(o + c) = w2;
+    }
+  }
+}
+
+// ---- LayerNorm in place over bf16 rows ----------------------------------------------------------
+__global__ void __launch_bounds__(256)
+layernorm_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                 const float* __restrict__ beta, float eps, int rows, int hidden) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  __nv_bfloat16* xr = x + static_cast<size_t>(row) * hidden;
+  const int nvec = hidden >> 7;
+  float4 v[MAX_VEC];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    if (i < nvec) {
+      const uint2 raw = *reinterpret_cast<const uint2*>(xr + i * 128 + lane * 4);
+      v[i] = make_float4(bf16_lo(raw.x), bf16_hi(raw.x), bf16_lo(raw.y), bf16_hi(raw.y));
+      sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
+  }
+  const float mean = warp_sum(sum) / hidden;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    if (i < nvec) {
+      const float dx = v[i].x - mean, dy = v[i].y - mean, dz = v[i].z - mean, dw = v[i].w - mean;
+      sq += (dx * dx + dy * dy) + (dz * dz + dw * dw);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / hidden + eps);
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    if (i < nvec) {
+      const int c = i * 128 + lane * 4;
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
+      const float4 bb = __ldg(reinterpret_cast<const float4*>(beta + c));
+      uint2 w2;
+      w2.x = pack_bf16x2((v[i].x - mean) * rstd * g.x + bb.x, (v[i].y - mean) * rstd * g.y + bb.y);
+      w2.y = pack_bf16x2((v[i].z - mean) * rstd * g.z + bb.z, (v[i].w - mean) * rstd * g.w + bb.w);
+      *reinterpret_cast<uint2*>(xr + c) = w2;
+    }
+  }
+}
+
+// ---- classifier head ----------------------------------------------------------------------------
+// One warp per item. logits in shared memory (C floats per warp), then softmax, top-k by repeated
+// arg-max (k and C are small: the contract's default is k = 5), label = arg-max, histogram.
+constexpr int HEAD_WARPS = 4;
+
+__global__ void __launch_bounds__(HEAD_WARPS * 32)
+classify_head_kernel(const __nv_bfloat16* __restrict__ pooled, int ld_pooled,
+                     const float* __restrict__ Wc, const float* __restrict__ bc, int B, int hidden,
+                     int C, int topk, float* __restrict__ logits_out, int32_t* __restrict__ top_idx,
+                     float* __restrict__ top_score, int32_t* __restrict__ labels,
+                     unsigned long long* __restrict__ histogram) {
+  extern __shared__ float head_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int item = blockIdx.x * HEAD_WARPS + warp;
+  if (item >= B) return;
+  float* lg = head_smem + warp * C;
+  const __nv_bfloat16* x = pooled + static_cast<size_t>(item) * ld_pooled;
+
+  for (int c = 0; c < C; ++c) {
+    const float* w = Wc + static_cast<size_t>(c) * hidden;
+    float acc = 0.f;
+    for (int k = lane * 4; k < hidden; k += 128) {
+      const uint2 raw = *reinterpret_cast<const uint2*>(x + k);
+      const float4 ww = __ldg(reinterpret_cast<const float4*>(w + k));
+      acc = fmaf(bf16_lo(raw.x), ww.x, acc);
+      acc = fmaf(bf16_hi(raw.x), ww.y, acc);
+      acc = fmaf(bf16_lo(raw.y), ww.z, acc);
+      acc = fmaf(bf16_hi(raw.y), ww.w, acc);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) lg[c] = acc + bc[c];
+  }
+  __syncwarp();
+  if (logits_out)
+    for (int c = lane; c < C; c += 32) logits_out[static_cast<size_t>(item) * C + c] = lg[c];
+
+  // softmax statistics
+  float mx = -INFINITY;
+  for (int c = lane; c < C; c += 32) mx = fmaxf(mx, lg[c]);
+  mx = warp_max(mx);
+  float den = 0.f;
+  for (int c = lane; c < C; c += 32) den += __expf(lg[c] - mx);
+  den = warp_sum(den);
+  const float inv = 1.0f / den;
+
+  // top-k: k rounds of (max value, lowest index) over the not-yet-taken classes
+  for (int t = 0; t < topk; ++t) {
+    float best = -INFINITY;
+    int best_i = 0x7fffffff;
+    for (int c = lane; c < C; c += 32) {
+      const float v = lg[c];
+      if (v > best || (v == best && c < best_i)) { best = v; best_i = c; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+      if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+    }
+    if (lane == 0) {
+      top_idx[static_cast<size_t>(item) * topk + t] = best_i;
+      top_score[static_cast<size_t>(item) * topk + t] = __expf(best - mx) * inv;
+      if (t == 0) {
+        labels[item] = best_i;
+        if (histogram) atomicAdd(histogram + best_i, 1ull);
+      }
+      lg[best_i] = -INFINITY;  // logits were already copied out above
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void mask_to_lens_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ lens,
+                                    int B, int S) {
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  const int lane = threadIdx.x & 31;
+  int n = 0;
+  for (int s = lane; s < S; s += 32) n += mask[static_cast<size_t>(b) * S + s] != 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if (lane == 0) lens[b] = n;
+}
+
+}  // namespace
+
+int embed_layernorm(cudaStream_t stream, const int32_t* ids, const float* word, const float* pos,
+                    const float* type0, const float* gamma, const float* beta, float eps,
+                    __nv_bfloat16* out, int rows, int S, int hidden, int vocab) {
+  if ((hidden % 128) != 0 || hidden > MAX_VEC * 128) {
+    set_last_error("embed_layernorm: hidden must be a multiple of 128 and <= %d", MAX_VEC * 128);
+    return B2_ERR_ARG;
+  }
+  if (rows <= 0) return B2_OK;
+  const int wpb = 8;
+  embed_ln_kernel<<<(rows + wpb - 1) / wpb, wpb * 32, 0, stream>>>(ids, word, pos, type0, gamma, beta,
+                                                                  eps, out, rows, S, hidden, vocab);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int layernorm_inplace(cudaStream_t stream, __nv_bfloat16* x, const float* gamma, const float* beta,
+                      float eps, int rows, int hidden) {
+  if ((hidden % 128) != 0 || hidden > MAX_VEC * 128) {
+    set_last_error("layernorm_inplace: hidden must be a multiple of 128 and <= %d", MAX_VEC * 128);
+    return B2_ERR_ARG;
+  }
+  if (rows <= 0) return B2_OK;
+  const int wpb = 8;
+  layernorm_kernel<<<(rows + wpb - 1) / wpb, wpb * 32, 0, stream>>>(x, gamma, beta, eps, rows, hidden);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int classify_head(cudaStream_t stream, const __nv_bfloat16* pooled, int ld_pooled, const float* Wc,
+                  const float* bc, int B, int hidden, int C, int topk, float* logits,
+                  int32_t* top_idx, float* top_score, int32_t* labels,
+                  unsigned long long* histogram) {
+  if (C <= 0 || C > 2048 || topk < 1 || topk > C || (hidden % 4) != 0 || (ld_pooled % 4) != 0) {
+    set_last_error("classify_head: need 1 <= topk <= C <= 2048 and hidden %% 4 == 0 (C=%d topk=%d)", C,
+                   topk);
+    return B2_ERR_ARG;
+  }
+  if (B <= 0) return B2_OK;
+  const size_t smem = static_cast<size_t>(HEAD_WARPS) * C * sizeof(float);
+  classify_head_kernel<<<(B + HEAD_WARPS - 1) / HEAD_WARPS, HEAD_WARPS * 32, smem, stream>>>(
+      pooled, ld_pooled, Wc, bc, B, hidden, C, topk, logits, top_idx, top_score, labels, histogram);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B, int S) {
+  if (B <= 0) return B2_OK;
+  mask_to_lens_kernel<<<(B + 7) / 8, 256, 0, stream>>>(mask, lens, B, S);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+}  // namespace b2

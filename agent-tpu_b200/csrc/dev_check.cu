@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include <algorithm>
 
 #include "b2_kernels.h"
 
@@ -103,6 +104,185 @@ static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it) {
   return bad ? 1 : 0;
 }
 
+static int check_attention(int B, int S, int hidden, const std::vector<int>& lens_in, bool time_it) {
+  const int rows = B * S, heads = hidden / 64;
+  std::vector<float> f((size_t)rows * 3 * hidden);
+  std::vector<__nv_bfloat16> hq(f.size());
+  for (size_t i = 0; i < f.size(); ++i) { f[i] = bf16_round(frand() * 2.0f); hq[i] = __float2bfloat16(f[i]); }
+  std::vector<int32_t> lens(B);
+  for (int b = 0; b < B; ++b) lens[b] = lens_in[b % lens_in.size()];
+  __nv_bfloat16 *dq, *dout;
+  int32_t* dl;
+  CK(cudaMalloc(&dq, hq.size() * 2));
+  CK(cudaMalloc(&dout, (size_t)rows * hidden * 2));
+  CK(cudaMalloc(&dl, B * 4));
+  CK(cudaMemcpy(dq, hq.data(), hq.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dl, lens.data(), B * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemset(dout, 0xFF, (size_t)rows * hidden * 2));
+  CUtensorMap tq;
+  B2(attention_tmap_qkv(&tq, dq, rows, hidden));
+  B2(attention_bf16(0, tq, dout, dl, B, S, hidden));
+  CK(cudaDeviceSynchronize());
+  std::vector<__nv_bfloat16> ho((size_t)rows * hidden);
+  CK(cudaMemcpy(ho.data(), dout, ho.size() * 2, cudaMemcpyDeviceToHost));
+  double max_err = 0; size_t bad = 0, checked = 0;
+  const int ld = 3 * hidden;
+  int bstep = B > 8 ? B / 8 : 1;
+  for (int b = 0; b < B; b += bstep) for (int h = 0; h < heads; ++h) {
+    int len = lens[b];
+    for (int qi = 0; qi < S; qi += (S > 128 ? 7 : 3)) {
+      const float* q = &f[(size_t)(b * S + qi) * ld + h * 64];
+      std::vector<double> sc(len);
+      double mx = -1e300;
+      for (int j = 0; j < len; ++j) {
+        const float* k = &f[(size_t)(b * S + j) * ld + hidden + h * 64];
+        double a = 0; for (int d = 0; d < 64; ++d) a += (double)q[d] * k[d];
+        sc[j] = a * 0.125; mx = std::max(mx, sc[j]);
+      }
+      double den = 0; for (int j = 0; j < len; ++j) { sc[j] = exp(sc[j] - mx); den += sc[j]; }
+      for (int d = 0; d < 64; ++d) {
+        double a = 0;
+        for (int j = 0; j < len; ++j) a += sc[j] * f[(size_t)(b * S + j) * ld + 2 * hidden + h * 64 + d];
+        a = len > 0 ? a / den : 0.0;
+        double got = __bfloat162float(ho[(size_t)(b * S + qi) * hidden + h * 64 + d]);
+        double err = fabs(got - a);
+        if (!(err <= 0.02 + 0.02 * fabs(a))) { if (bad < 5) printf("  mismatch b=%d h=%d q=%d d=%d got=%f want=%f\n", b, h, qi, d, got, a); ++bad; }
+        max_err = std::max(max_err, err); ++checked;
+      }
+    }
+  }
+  printf("attention B=%d S=%d H=%d: checked=%zu bad=%zu max_abs_err=%.5f %s\n", B, S, hidden, checked, bad, max_err, bad ? "FAIL" : "ok");
+  if (time_it && !bad) {
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (int i = 0; i < 3; ++i) B2(attention_bf16(0, tq, dout, dl, B, S, hidden));
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < 10; ++i) B2(attention_bf16(0, tq, dout, dl, B, S, hidden));
+    CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= 10;
+    double bytes = (double)rows * hidden * 2 * 4;
+    printf("  time %.3f ms  %.1f GB/s (Q,K,V,O once)\n", ms, bytes / ms / 1e6);
+  }
+  cudaFree(dq); cudaFree(dout); cudaFree(dl);
+  return bad ? 1 : 0;
+}
+
+static int check_rows(int rows, int S, int hidden, int vocab, bool time_it) {
+  int fails = 0;
+  std::vector<float> word((size_t)vocab * hidden), pos((size_t)S * hidden), type0(hidden), g(hidden), bt(hidden);
+  for (auto& v : word) v = frand(); for (auto& v : pos) v = frand(); for (auto& v : type0) v = frand();
+  for (auto& v : g) v = 1.0f + 0.3f * frand(); for (auto& v : bt) v = 0.2f * frand();
+  std::vector<int32_t> ids(rows); for (auto& v : ids) v = (int)((frand() * 0.5f + 0.5f) * (vocab - 1));
+  float *dw, *dp, *dt, *dg, *db; int32_t* di; __nv_bfloat16* dout;
+  CK(cudaMalloc(&dw, word.size() * 4)); CK(cudaMalloc(&dp, pos.size() * 4)); CK(cudaMalloc(&dt, hidden * 4));
+  CK(cudaMalloc(&dg, hidden * 4)); CK(cudaMalloc(&db, hidden * 4)); CK(cudaMalloc(&di, rows * 4));
+  CK(cudaMalloc(&dout, (size_t)rows * hidden * 2));
+  CK(cudaMemcpy(dw, word.data(), word.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dp, pos.data(), pos.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dt, type0.data(), hidden * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dg, g.data(), hidden * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(db, bt.data(), hidden * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(di, ids.data(), rows * 4, cudaMemcpyHostToDevice));
+  B2(embed_layernorm(0, di, dw, dp, dt, dg, db, 1e-12f, dout, rows, S, hidden, vocab));
+  CK(cudaDeviceSynchronize());
+  std::vector<__nv_bfloat16> ho((size_t)rows * hidden);
+  CK(cudaMemcpy(ho.data(), dout, ho.size() * 2, cudaMemcpyDeviceToHost));
+  size_t bad = 0; double max_err = 0;
+  std::vector<double> x(hidden);
+  for (int r = 0; r < rows; r += std::max(1, rows / 200)) {
+    double mean = 0;
+    for (int c = 0; c < hidden; ++c) { x[c] = (double)word[(size_t)ids[r] * hidden + c] + pos[(size_t)(r % S) * hidden + c] + type0[c]; mean += x[c]; }
+    mean /= hidden; double var = 0; for (int c = 0; c < hidden; ++c) var += (x[c] - mean) * (x[c] - mean); var /= hidden;
+    for (int c = 0; c < hidden; ++c) {
+      double want = (x[c] - mean) / sqrt(var + 1e-12) * g[c] + bt[c];
+      double got = __bfloat162float(ho[(size_t)r * hidden + c]);
+      double err = fabs(got - want); max_err = std::max(max_err, err);
+      if (!(err <= 0.01 + 0.01 * fabs(want))) ++bad;
+    }
+  }
+  printf("embed+LN rows=%d H=%d: bad=%zu max_abs_err=%.5f %s\n", rows, hidden, bad, max_err, bad ? "FAIL" : "ok");
+  fails += bad ? 1 : 0;
+  // in-place LN on the embed output (already bf16): compare with host LN of the bf16 values
+  B2(layernorm_inplace(0, dout, dg, db, 1e-12f, rows, hidden));
+  CK(cudaDeviceSynchronize());
+  std::vector<__nv_bfloat16> h2((size_t)rows * hidden);
+  CK(cudaMemcpy(h2.data(), dout, h2.size() * 2, cudaMemcpyDeviceToHost));
+  bad = 0; max_err = 0;
+  for (int r = 0; r < rows; r += std::max(1, rows / 200)) {
+    double mean = 0;
+    for (int c = 0; c < hidden; ++c) { x[c] = __bfloat162float(ho[(size_t)r * hidden + c]); mean += x[c]; }
+    mean /= hidden; double var = 0; for (int c = 0; c < hidden; ++c) var += (x[c] - mean) * (x[c] - mean); var /= hidden;
+    for (int c = 0; c < hidden; ++c) {
+      double want = (x[c] - mean) / sqrt(var + 1e-12) * g[c] + bt[c];
+      double got = __bfloat162float(h2[(size_t)r * hidden + c]);
+      double err = fabs(got - want); max_err = std::max(max_err, err);
+      if (!(err <= 0.01 + 0.01 * fabs(want))) ++bad;
+    }
+  }
+  printf("layernorm rows=%d H=%d: bad=%zu max_abs_err=%.5f %s\n", rows, hidden, bad, max_err, bad ? "FAIL" : "ok");
+  fails += bad ? 1 : 0;
+  if (time_it) {
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (int i = 0; i < 3; ++i) B2(layernorm_inplace(0, dout, dg, db, 1e-12f, rows, hidden));
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < 10; ++i) B2(layernorm_inplace(0, dout, dg, db, 1e-12f, rows, hidden));
+    CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= 10;
+    printf("  layernorm time %.3f ms  %.1f GB/s\n", ms, (double)rows * hidden * 4 / ms / 1e6);
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < 10; ++i) B2(embed_layernorm(0, di, dw, dp, dt, dg, db, 1e-12f, dout, rows, S, hidden, vocab));
+    CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+    CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= 10;
+    printf("  embed+LN time %.3f ms\n", ms);
+  }
+  cudaFree(dw); cudaFree(dp); cudaFree(dt); cudaFree(dg); cudaFree(db); cudaFree(di); cudaFree(dout);
+  return fails;
+}
+
+static int check_head(int B, int hidden, int C, int topk) {
+  std::vector<float> fp((size_t)B * hidden), W((size_t)C * hidden), bc(C);
+  std::vector<__nv_bfloat16> hp(fp.size());
+  for (size_t i = 0; i < fp.size(); ++i) { fp[i] = bf16_round(frand()); hp[i] = __float2bfloat16(fp[i]); }
+  for (auto& v : W) v = frand() * 0.2f; for (auto& v : bc) v = frand();
+  __nv_bfloat16* dp; float *dW, *dbc, *dlog, *dts; int32_t *dti, *dlab; unsigned long long* dh;
+  CK(cudaMalloc(&dp, hp.size() * 2)); CK(cudaMalloc(&dW, W.size() * 4)); CK(cudaMalloc(&dbc, C * 4));
+  CK(cudaMalloc(&dlog, (size_t)B * C * 4)); CK(cudaMalloc(&dts, (size_t)B * topk * 4)); CK(cudaMalloc(&dti, (size_t)B * topk * 4));
+  CK(cudaMalloc(&dlab, B * 4)); CK(cudaMalloc(&dh, C * 8)); CK(cudaMemset(dh, 0, C * 8));
+  CK(cudaMemcpy(dp, hp.data(), hp.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dW, W.data(), W.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dbc, bc.data(), C * 4, cudaMemcpyHostToDevice));
+  B2(classify_head(0, dp, hidden, dW, dbc, B, hidden, C, topk, dlog, dti, dts, dlab, dh));
+  CK(cudaDeviceSynchronize());
+  std::vector<float> lg((size_t)B * C), ts((size_t)B * topk); std::vector<int32_t> ti((size_t)B * topk), lab(B);
+  std::vector<unsigned long long> hist(C);
+  CK(cudaMemcpy(lg.data(), dlog, lg.size() * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(ts.data(), dts, ts.size() * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(ti.data(), dti, ti.size() * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(lab.data(), dlab, B * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(hist.data(), dh, C * 8, cudaMemcpyDeviceToHost));
+  size_t bad = 0; std::vector<unsigned long long> hh(C, 0);
+  for (int b = 0; b < B; ++b) {
+    std::vector<double> l(C);
+    for (int c = 0; c < C; ++c) { double a = bc[c]; for (int k = 0; k < hidden; ++k) a += (double)fp[(size_t)b * hidden + k] * W[(size_t)c * hidden + k]; l[c] = a;
+      if (fabs(a - lg[(size_t)b * C + c]) > 1e-3) ++bad; }
+    // top-k from the device logits themselves (exact ordering check)
+    std::vector<int> order(C); for (int c = 0; c < C; ++c) order[c] = c;
+    const float* dl = &lg[(size_t)b * C];
+    std::stable_sort(order.begin(), order.end(), [&](int a, int c) { return dl[a] > dl[c]; });
+    double mx = dl[order[0]], den = 0; for (int c = 0; c < C; ++c) den += exp((double)dl[c] - mx);
+    for (int t = 0; t < topk; ++t) {
+      if (ti[(size_t)b * topk + t] != order[t]) ++bad;
+      double want = exp((double)dl[order[t]] - mx) / den;
+      if (fabs(want - ts[(size_t)b * topk + t]) > 1e-5) ++bad;
+    }
+    if (lab[b] != order[0]) ++bad;
+    hh[order[0]]++;
+  }
+  for (int c = 0; c < C; ++c) if (hh[c] != hist[c]) ++bad;
+  printf("head B=%d H=%d C=%d k=%d: bad=%zu %s\n", B, hidden, C, topk, bad, bad ? "FAIL" : "ok");
+  cudaFree(dp); cudaFree(dW); cudaFree(dbc); cudaFree(dlog); cudaFree(dts); cudaFree(dti); cudaFree(dlab); cudaFree(dh);
+  return bad ? 1 : 0;
+}
+
 int main(int argc, char** argv) {
   const char* what = argc > 1 ? argv[1] : "all";
   int dev = 0;
@@ -127,6 +307,23 @@ int main(int argc, char** argv) {
     fails += check_gemm(131072, 768, 768, GEMM_EPI_BIAS_RESIDUAL, sms, true);
     fails += check_gemm(131072, 3072, 768, GEMM_EPI_BIAS_GELU, sms, true);
     fails += check_gemm(131072, 768, 3072, GEMM_EPI_BIAS_RESIDUAL, sms, true);
+  }
+  if (!strcmp(what, "all") || !strcmp(what, "attn")) {
+    fails += check_attention(3, 128, 128, {128, 37, 2}, false);
+    fails += check_attention(5, 512, 128, {512, 300, 129, 5, 128}, false);
+    fails += check_attention(64, 128, 768, {128, 16, 77, 100}, false);
+  }
+  if (!strcmp(what, "all") || !strcmp(what, "attnperf")) {
+    fails += check_attention(1024, 128, 768, {128}, true);
+    fails += check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, true);
+    fails += check_attention(256, 512, 768, {512, 300}, true);
+  }
+  if (!strcmp(what, "all") || !strcmp(what, "rows")) {
+    fails += check_rows(1000, 128, 128, 500, false);
+    fails += check_rows(131072, 128, 768, 30522, true);
+    fails += check_head(1000, 768, 16, 5);
+    fails += check_head(77, 128, 3, 3);
+    fails += check_head(50, 768, 1000, 5);
   }
   printf("%s (%d failing checks)\n", fails ? "DEV_CHECK FAILED" : "DEV_CHECK PASSED", fails);
   return fails ? 1 : 0;
