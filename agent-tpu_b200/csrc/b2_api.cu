@@ -1,0 +1,909 @@
+// b2_api.cu — the exported C ABI (include/b2_classify.h): handle life cycle, model file loading,
+// and the per-job orchestration of the kernels (tokenize -> embed+LN -> 12 x {QKV GEMM, attention,
+// out-proj GEMM + residual, LN, FFN1 GEMM + GELU, FFN2 GEMM + residual, LN} -> pooler GEMM + tanh
+// -> head).
+//
+// It is the B200 counterpart of get_tpu_handle (ops/_tpu_runtime.py:34-63: load once, cache, check
+// the file exists) and of the set_tensor / invoke / get_tensor / _topk sequence in
+// ops/map_classify_tpu.py:61-75, widened from one tensor per call to a whole job of items.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "b2_tokenizer.h"
+
+namespace b2 {
+
+namespace {
+
+// ---- model file (.b2m) ---------------------------------------------------------------------------
+// header, little endian (written by agent-tpu_b200/model_file.py):
+//   char magic[4] = "B2MD"; u32 version = 1;
+//   u32 hidden, layers, heads, intermediate, vocab_size, max_positions, type_vocab, num_labels;
+//   f32 ln_eps; u32 kind (0 = f32 tensors follow, 1 = synthetic); u64 seed;
+//   f32 init_std, bias_std, gamma_std, classifier_std;
+// kind 0: the tensors follow in the order of `tensor_list()` below, f32.
+// kind 1: tensor t, element i = scale_t * (sum of 16-bit lanes of splitmix64(seed, t, i) - 131070)
+//         + shift_t, with scale_t = std_t / sqrt(4 * (65536^2 - 1) / 12)  (see b2_weights.cu).
+struct ModelHeader {
+  char magic[4];
+  uint32_t version;
+  uint32_t hidden, layers, heads, intermediate, vocab_size, max_positions, type_vocab, num_labels;
+  float ln_eps;
+  uint32_t kind;
+  uint64_t seed;
+  float init_std, bias_std, gamma_std, classifier_std;
+};
+static_assert(sizeof(ModelHeader) == 72, "model header layout");
+
+enum TensorRole { ROLE_WEIGHT, ROLE_BIAS, ROLE_GAMMA, ROLE_BETA, ROLE_CLASSIFIER };
+
+struct TensorSpec {
+  uint32_t id;     // stable tensor id (hash stream selector for synthetic models)
+  int64_t n;       // elements
+  TensorRole role;
+};
+
+// ids: 0 word, 1 pos, 2 type, 3 emb_ln_g, 4 emb_ln_b, 8 Wp, 9 bp, 10 Wc, 11 bc,
+//      layer l: 16 + 16*l + {0 Wqkv, 1 bqkv, 2 Wo, 3 bo, 4 ln1_g, 5 ln1_b, 6 W1, 7 b1, 8 W2, 9 b2,
+//                            10 ln2_g, 11 ln2_b}
+std::vector<TensorSpec> tensor_list(const ModelHeader& m) {
+  const int64_t H = m.hidden, I = m.intermediate;
+  std::vector<TensorSpec> t;
+  t.push_back({0, int64_t(m.vocab_size) * H, ROLE_WEIGHT});
+  t.push_back({1, int64_t(m.max_positions) * H, ROLE_WEIGHT});
+  t.push_back({2, int64_t(m.type_vocab) * H, ROLE_WEIGHT});
+  t.push_back({3, H, ROLE_GAMMA});
+  t.push_back({4, H, ROLE_BETA});
+  for (uint32_t l = 0; l < m.layers; ++l) {
+    const uint32_t b = 16 + 16 * l;
+    t.push_back({b + 0, 3 * H * H, ROLE_WEIGHT});
+    t.push_back({b + 1, 3 * H, ROLE_BIAS});
+    t.push_back({b + 2, H * H, ROLE_WEIGHT});
+    t.push_back({b + 3, H, ROLE_BIAS});
+    t.push_back({b + 4, H, ROLE_GAMMA});
+    t.push_back({b + 5, H, ROLE_BETA});
+    t.push_back({b + 6, I * H, ROLE_WEIGHT});
+    t.push_back({b + 7, I, ROLE_BIAS});
+    t.push_back({b + 8, H * I, ROLE_WEIGHT});
+    t.push_back({b + 9, H, ROLE_BIAS});
+    t.push_back({b + 10, H, ROLE_GAMMA});
+    t.push_back({b + 11, H, ROLE_BETA});
+  }
+  t.push_back({8, H * H, ROLE_WEIGHT});
+  t.push_back({9, H, ROLE_BIAS});
+  t.push_back({10, int64_t(m.num_labels) * H, ROLE_CLASSIFIER});
+  t.push_back({11, int64_t(m.num_labels), ROLE_BIAS});
+  return t;
+}
+
+struct LayerWeights {
+  __nv_bfloat16 *Wqkv, *Wo, *W1, *W2;
+  float *bqkv, *bo, *b1, *b2, *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+  CUtensorMap tm_qkv, tm_o, tm_1, tm_2;
+};
+
+enum Kind {
+  K_TOKENIZE, K_EMBED, K_GEMM_QKV, K_ATTENTION, K_GEMM_OUT, K_LAYERNORM, K_GEMM_FFN1, K_GEMM_FFN2,
+  K_POOLER, K_HEAD, K_COUNT
+};
+
+}  // namespace
+}  // namespace b2
+
+using namespace b2;
+
+struct b2_handle {
+  int device = 0;
+  int num_sms = 0;
+  cudaStream_t stream = nullptr;
+  std::mutex mu;
+
+  bool has_tokenizer = false;
+  TokenizerDev tok{};
+  int tok_vocab = 0;
+
+  bool has_model = false;
+  ModelHeader mh{};
+  float *word = nullptr, *pos = nullptr, *type0 = nullptr, *emb_g = nullptr, *emb_b = nullptr;
+  std::vector<LayerWeights> layers;
+  __nv_bfloat16* Wp = nullptr;
+  float *bp = nullptr, *Wc = nullptr, *bc = nullptr;
+  CUtensorMap tm_p{};
+  int64_t weight_bytes = 0, activation_bytes = 0;
+  std::vector<void*> allocations;
+
+  int max_batch = 1024, max_len = 128;
+  // activations for one batch (rows = max_batch * max_len)
+  int32_t *ids = nullptr, *lens = nullptr;
+  uint8_t* mask = nullptr;
+  __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *ffn = nullptr,
+                *pooled = nullptr;
+  CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{}, tm_att{};
+  unsigned long long* hist = nullptr;
+  int64_t* d_tokens = nullptr;  // running sum of lens
+
+  // growable staging for host-pointer calls
+  uint8_t* st_text = nullptr; size_t st_text_cap = 0;
+  int64_t* st_off = nullptr; size_t st_off_cap = 0;
+  void* st_out = nullptr; size_t st_out_cap = 0;
+
+  // profiling
+  bool profiling = false;
+  std::vector<cudaEvent_t> events;
+  std::vector<int> event_kinds;
+  size_t n_events = 0;
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+};
+
+namespace b2 {
+namespace {
+
+int dev_alloc(b2_handle* h, void** p, size_t bytes) {
+  B2_CUDA_OK(cudaMalloc(p, bytes ? bytes : 16));
+  h->allocations.push_back(*p);
+  return B2_OK;
+}
+
+int grow(void** p, size_t* cap, size_t need) {
+  if (need <= *cap) return B2_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr;
+  *cap = 0;
+  size_t want = need + need / 4 + 4096;
+  B2_CUDA_OK(cudaMalloc(p, want));
+  *cap = want;
+  return B2_OK;
+}
+
+float synth_scale(float std_dev) {
+  // std of the sum of four independent uniform integers in [0, 65535]
+  const double sd = sqrt(4.0 * (65536.0 * 65536.0 - 1.0) / 12.0);
+  return static_cast<float>(static_cast<double>(std_dev) / sd);
+}
+
+// mark: profiling boundary before a launch of kind `k`
+void mark(b2_handle* h, int kind) {
+  if (!h->profiling) return;
+  if (h->n_events == h->events.size()) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    h->events.push_back(e);
+    h->event_kinds.push_back(0);
+  }
+  h->event_kinds[h->n_events] = kind;
+  cudaEventRecord(h->events[h->n_events], h->stream);
+  h->n_events++;
+}
+
+struct KindAcc {
+  double ms[K_COUNT] = {};
+  int64_t n[K_COUNT] = {};
+  int64_t launches = 0;
+};
+
+// close the current profiling segment list: events[i] .. events[i+1] brackets a launch of kind[i]
+int flush_profile(b2_handle* h, KindAcc* acc) {
+  if (!h->profiling || h->n_events == 0) return B2_OK;
+  mark(h, -1);
+  B2_CUDA_OK(cudaStreamSynchronize(h->stream));
+  for (size_t i = 0; i + 1 < h->n_events; ++i) {
+    float ms = 0.f;
+    B2_CUDA_OK(cudaEventElapsedTime(&ms, h->events[i], h->events[i + 1]));
+    const int k = h->event_kinds[i];
+    if (k >= 0 && k < K_COUNT) { acc->ms[k] += ms; acc->n[k] += 1; }
+  }
+  h->n_events = 0;
+  return B2_OK;
+}
+
+int load_model(b2_handle* h, const char* path) {
+  FILE* f = fopen(path, "rb");
+  if (!f) {
+    set_last_error("model file not found: %s", path);
+    return B2_ERR_IO;
+  }
+  ModelHeader& m = h->mh;
+  if (fread(&m, sizeof(m), 1, f) != 1 || memcmp(m.magic, "B2MD", 4) != 0 || m.version != 1) {
+    fclose(f);
+    set_last_error("'%s' is not a B2MD v1 model file", path);
+    return B2_ERR_FORMAT;
+  }
+  if (m.hidden == 0 || m.hidden % 128 != 0 || m.hidden > 1024 || m.heads * 64 != m.hidden ||
+      m.intermediate % 8 != 0 || m.layers == 0 || m.num_labels == 0 || m.num_labels > 2048 ||
+      m.type_vocab == 0 || m.vocab_size == 0 || m.kind > 1) {
+    fclose(f);
+    set_last_error("model '%s': unsupported geometry (hidden=%u must be a multiple of 128 and <= 1024 "
+                   "with head dim 64; heads=%u intermediate=%u labels=%u)",
+                   path, m.hidden, m.heads, m.intermediate, m.num_labels);
+    return B2_ERR_FORMAT;
+  }
+  const std::vector<TensorSpec> specs = tensor_list(m);
+  int64_t max_n = 0;
+  for (const auto& s : specs) max_n = std::max(max_n, s.n);
+  float* scratch = nullptr;  // f32 staging for tensors that are stored as bf16
+  B2_CUDA_OK(cudaMalloc(&scratch, max_n * sizeof(float)));
+  std::vector<float> host;
+  h->layers.resize(m.layers);
+  int rc = B2_OK;
+
+  auto materialise = [&](const TensorSpec& s, float* dst) -> int {
+    if (m.kind == 1) {
+      float sd = 0.f, shift = 0.f;
+      switch (s.role) {
+        case ROLE_WEIGHT: sd = m.init_std; break;
+        case ROLE_BIAS: sd = m.bias_std; break;
+        case ROLE_GAMMA: sd = m.gamma_std; shift = 1.0f; break;
+        case ROLE_BETA: sd = m.bias_std; break;
+        case ROLE_CLASSIFIER: sd = m.classifier_std; break;
+      }
+      return fill_synthetic_f32(h->stream, dst, s.n, m.seed, s.id, synth_scale(sd), shift);
+    }
+    host.resize(s.n);
+    if (fread(host.data(), sizeof(float), s.n, f) != static_cast<size_t>(s.n)) {
+      set_last_error("model '%s' is truncated (tensor id %u)", path, s.id);
+      return B2_ERR_FORMAT;
+    }
+    B2_CUDA_OK(cudaMemcpyAsync(dst, host.data(), s.n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    B2_CUDA_OK(cudaStreamSynchronize(h->stream));
+    return B2_OK;
+  };
+  auto want_f32 = [&](const TensorSpec& s, float** out) -> int {
+    if ((rc = dev_alloc(h, reinterpret_cast<void**>(out), s.n * sizeof(float)))) return rc;
+    h->weight_bytes += s.n * sizeof(float);
+    return materialise(s, *out);
+  };
+  auto want_bf16 = [&](const TensorSpec& s, __nv_bfloat16** out) -> int {
+    if ((rc = dev_alloc(h, reinterpret_cast<void**>(out), s.n * sizeof(__nv_bfloat16)))) return rc;
+    h->weight_bytes += s.n * sizeof(__nv_bfloat16);
+    if ((rc = materialise(s, scratch))) return rc;
+    return convert_f32_to_bf16(h->stream, scratch, *out, s.n);
+  };
+
+  size_t k = 0;
+  do {
+    if ((rc = want_f32(specs[k++], &h->word))) break;
+    if ((rc = want_f32(specs[k++], &h->pos))) break;
+    if ((rc = want_f32(specs[k++], &h->type0))) break;
+    if ((rc = want_f32(specs[k++], &h->emb_g))) break;
+    if ((rc = want_f32(specs[k++], &h->emb_b))) break;
+    for (uint32_t l = 0; l < m.layers && !rc; ++l) {
+      LayerWeights& L = h->layers[l];
+      if ((rc = want_bf16(specs[k++], &L.Wqkv))) break;
+      if ((rc = want_f32(specs[k++], &L.bqkv))) break;
+      if ((rc = want_bf16(specs[k++], &L.Wo))) break;
+      if ((rc = want_f32(specs[k++], &L.bo))) break;
+      if ((rc = want_f32(specs[k++], &L.ln1_g))) break;
+      if ((rc = want_f32(specs[k++], &L.ln1_b))) break;
+      if ((rc = want_bf16(specs[k++], &L.W1))) break;
+      if ((rc = want_f32(specs[k++], &L.b1))) break;
+      if ((rc = want_bf16(specs[k++], &L.W2))) break;
+      if ((rc = want_f32(specs[k++], &L.b2))) break;
+      if ((rc = want_f32(specs[k++], &L.ln2_g))) break;
+      if ((rc = want_f32(specs[k++], &L.ln2_b))) break;
+      const int H = m.hidden, I = m.intermediate;
+      if ((rc = gemm_tmap_b(&L.tm_qkv, L.Wqkv, 3 * H, H))) break;
+      if ((rc = gemm_tmap_b(&L.tm_o, L.Wo, H, H))) break;
+      if ((rc = gemm_tmap_b(&L.tm_1, L.W1, I, H))) break;
+      if ((rc = gemm_tmap_b(&L.tm_2, L.W2, H, I))) break;
+    }
+    if (rc) break;
+    if ((rc = want_bf16(specs[k++], &h->Wp))) break;
+    if ((rc = want_f32(specs[k++], &h->bp))) break;
+    if ((rc = want_f32(specs[k++], &h->Wc))) break;
+    if ((rc = want_f32(specs[k++], &h->bc))) break;
+    if ((rc = gemm_tmap_b(&h->tm_p, h->Wp, m.hidden, m.hidden))) break;
+  } while (0);
+  fclose(f);
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  cudaFree(scratch);
+  if (rc) return rc;
+  if (e != cudaSuccess) {
+    set_last_error("model load failed on device: %s", cudaGetErrorString(e));
+    return B2_ERR_CUDA;
+  }
+  h->has_model = true;
+  return B2_OK;
+}
+
+int alloc_activations(b2_handle* h) {
+  const ModelHeader& m = h->mh;
+  const int64_t rows = int64_t(h->max_batch) * h->max_len;
+  const int64_t H = m.hidden, I = m.intermediate;
+  int rc;
+  auto A = [&](void** p, int64_t bytes) { h->activation_bytes += bytes; return dev_alloc(h, p, bytes); };
+  if ((rc = A(reinterpret_cast<void**>(&h->ids), rows * 4))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->mask), rows))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->lens), h->max_batch * 4))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->d_tokens), 8))) return rc;
+  if (!h->has_model) return B2_OK;
+  if ((rc = A(reinterpret_cast<void**>(&h->x), rows * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->qkv), rows * 3 * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->ctx), rows * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->y), rows * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->ffn), rows * I * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->pooled), int64_t(h->max_batch) * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->hist), int64_t(m.num_labels) * 8))) return rc;
+  // pad rows are read by TMA boxes and attention tiles before they are ever written: give them
+  // finite contents once so no NaN bit pattern can reach a masked-out product
+  B2_CUDA_OK(cudaMemsetAsync(h->x, 0, rows * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->qkv, 0, rows * 3 * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->ctx, 0, rows * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->y, 0, rows * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->ffn, 0, rows * I * 2, h->stream));
+  if ((rc = gemm_tmap_a(&h->tm_x, h->x, rows, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&h->tm_ctx, h->ctx, rows, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&h->tm_y, h->y, rows, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&h->tm_ffn, h->ffn, rows, I, I))) return rc;
+  if ((rc = attention_tmap_qkv(&h->tm_att, h->qkv, rows, H))) return rc;
+  B2_CUDA_OK(cudaStreamSynchronize(h->stream));
+  return B2_OK;
+}
+
+__global__ void sum_lens_kernel(const int32_t* lens, int n, int64_t* total) {
+  long long s = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s += lens[i];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __shared__ long long part[32];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long t = 0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) t += part[w];
+    *total += t;
+  }
+}
+
+__global__ void hist_to_i64_kernel(const unsigned long long* src, int64_t* dst, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = static_cast<int64_t>(src[i]);
+}
+
+// Encoder + head for one batch whose ids / lens are already in h->ids / h->lens.
+int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, float* d_top_score,
+                  int32_t* d_labels, float* d_logits, int64_t* launches) {
+  const ModelHeader& m = h->mh;
+  const int H = m.hidden, I = m.intermediate, M = B * S;
+  cudaStream_t st = h->stream;
+  int rc;
+  mark(h, K_EMBED);
+  if ((rc = embed_layernorm(st, h->ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, h->x,
+                            M, S, H, m.vocab_size))) return rc;
+  ++*launches;
+  for (uint32_t l = 0; l < m.layers; ++l) {
+    LayerWeights& L = h->layers[l];
+    mark(h, K_GEMM_QKV);
+    if ((rc = gemm_bf16_tn(st, h->tm_x, L.tm_qkv, h->qkv, L.bqkv, nullptr, M, 3 * H, H, 3 * H, 0,
+                           GEMM_EPI_BIAS, h->num_sms))) return rc;
+    mark(h, K_ATTENTION);
+    if ((rc = attention_bf16(st, h->tm_att, h->ctx, h->lens, B, S, H))) return rc;
+    mark(h, K_GEMM_OUT);
+    if ((rc = gemm_bf16_tn(st, h->tm_ctx, L.tm_o, h->y, L.bo, h->x, M, H, H, H, H,
+                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
+    mark(h, K_LAYERNORM);
+    if ((rc = layernorm_inplace(st, h->y, L.ln1_g, L.ln1_b, m.ln_eps, M, H))) return rc;
+    mark(h, K_GEMM_FFN1);
+    if ((rc = gemm_bf16_tn(st, h->tm_y, L.tm_1, h->ffn, L.b1, nullptr, M, I, H, I, 0,
+                           GEMM_EPI_BIAS_GELU, h->num_sms))) return rc;
+    mark(h, K_GEMM_FFN2);
+    if ((rc = gemm_bf16_tn(st, h->tm_ffn, L.tm_2, h->x, L.b2, h->y, M, H, I, H, H,
+                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
+    mark(h, K_LAYERNORM);
+    if ((rc = layernorm_inplace(st, h->x, L.ln2_g, L.ln2_b, m.ln_eps, M, H))) return rc;
+    *launches += 7;
+  }
+  // pooler over the [CLS] rows: a strided view of x (row pitch S*H) through the A tensor map
+  CUtensorMap tm_cls;
+  if ((rc = gemm_tmap_a(&tm_cls, h->x, B, H, int64_t(S) * H))) return rc;
+  mark(h, K_POOLER);
+  if ((rc = gemm_bf16_tn(st, tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
+                         GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
+  mark(h, K_HEAD);
+  if ((rc = classify_head(st, h->pooled, H, h->Wc, h->bc, B, H, m.num_labels, topk, d_logits,
+                          d_top_idx, d_top_score, d_labels, h->hist))) return rc;
+  *launches += 2;
+  return B2_OK;
+}
+
+void fill_metrics(b2_metrics* out, const b2_handle* h, const KindAcc& acc, int64_t items,
+                  int64_t tokens, int64_t padded, int64_t batches, int64_t h2d, int64_t d2h,
+                  double gpu_ms) {
+  if (!out) return;
+  b2_metrics mtr;
+  memset(&mtr, 0, sizeof(mtr));
+  mtr.struct_size = sizeof(b2_metrics);
+  mtr.profiled = h->profiling ? 1 : 0;
+  mtr.items = items; mtr.tokens = tokens; mtr.padded_tokens = padded; mtr.batches = batches;
+  mtr.kernel_launches = acc.launches; mtr.h2d_bytes = h2d; mtr.d2h_bytes = d2h;
+  mtr.gpu_ms_total = gpu_ms;
+  mtr.ms_tokenize = acc.ms[K_TOKENIZE]; mtr.n_tokenize = acc.n[K_TOKENIZE];
+  mtr.ms_embed = acc.ms[K_EMBED]; mtr.n_embed = acc.n[K_EMBED];
+  mtr.ms_gemm_qkv = acc.ms[K_GEMM_QKV]; mtr.n_gemm_qkv = acc.n[K_GEMM_QKV];
+  mtr.ms_attention = acc.ms[K_ATTENTION]; mtr.n_attention = acc.n[K_ATTENTION];
+  mtr.ms_gemm_attn_out = acc.ms[K_GEMM_OUT]; mtr.n_gemm_attn_out = acc.n[K_GEMM_OUT];
+  mtr.ms_layernorm = acc.ms[K_LAYERNORM]; mtr.n_layernorm = acc.n[K_LAYERNORM];
+  mtr.ms_gemm_ffn1 = acc.ms[K_GEMM_FFN1]; mtr.n_gemm_ffn1 = acc.n[K_GEMM_FFN1];
+  mtr.ms_gemm_ffn2 = acc.ms[K_GEMM_FFN2]; mtr.n_gemm_ffn2 = acc.n[K_GEMM_FFN2];
+  mtr.ms_pooler = acc.ms[K_POOLER]; mtr.n_pooler = acc.n[K_POOLER];
+  mtr.ms_head = acc.ms[K_HEAD]; mtr.n_head = acc.n[K_HEAD];
+  const size_t n = std::min<size_t>(sizeof(mtr), out->struct_size > 0 ? out->struct_size : 0);
+  const int32_t keep = out->struct_size;
+  memcpy(out, &mtr, n);
+  out->struct_size = keep;
+}
+
+int check_len(const b2_handle* h, int32_t max_len, bool need_model) {
+  if (max_len < 2 || max_len > h->max_len) {
+    set_last_error("max_len %d is outside [2, %d] (the handle was created for max_len %d)", max_len,
+                   h->max_len, h->max_len);
+    return B2_ERR_LIMIT;
+  }
+  if (need_model) {
+    if (!h->has_model) {
+      set_last_error("this handle was created without a model (b2_config.model_path was NULL)");
+      return B2_ERR_ARG;
+    }
+    if (max_len % 128 != 0) {
+      set_last_error("classification needs max_len to be a multiple of 128 (got %d)", max_len);
+      return B2_ERR_ARG;
+    }
+    if (static_cast<uint32_t>(max_len) > h->mh.max_positions) {
+      set_last_error("max_len %d exceeds the model's %u positions", max_len, h->mh.max_positions);
+      return B2_ERR_LIMIT;
+    }
+  }
+  return B2_OK;
+}
+
+// Core of classification with everything in device memory. If d_utf8 is null, ids / mask rows are
+// taken from d_ids / d_mask instead of the tokenizer.
+int classify_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offsets,
+                    const int32_t* d_ids_in, const uint8_t* d_mask_in, int64_t n, int32_t max_len,
+                    int32_t topk, int32_t* d_top_idx, float* d_top_score, int32_t* d_labels,
+                    int64_t* d_hist, float* d_logits, b2_metrics* metrics, int64_t h2d, int64_t d2h) {
+  int rc;
+  if ((rc = check_len(h, max_len, true))) return rc;
+  const int C = h->mh.num_labels;
+  if (topk < 1 || topk > C) {
+    set_last_error("topk %d is outside [1, num_labels = %d]", topk, C);
+    return B2_ERR_ARG;
+  }
+  if (n < 0 || (n > 0 && (!d_top_idx || !d_top_score))) {
+    set_last_error("classify: n must be >= 0 and top_idx / top_score must not be NULL");
+    return B2_ERR_ARG;
+  }
+  if (d_utf8 && !h->has_tokenizer) {
+    set_last_error("this handle was created without a tokenizer (b2_config.vocab_path was NULL)");
+    return B2_ERR_ARG;
+  }
+  cudaStream_t st = h->stream;
+  KindAcc acc;
+  B2_CUDA_OK(cudaMemsetAsync(h->hist, 0, size_t(C) * 8, st));
+  B2_CUDA_OK(cudaMemsetAsync(h->d_tokens, 0, 8, st));
+  B2_CUDA_OK(cudaEventRecord(h->ev_begin, st));
+  int64_t batches = 0;
+  // labels are needed for the histogram even when the caller does not want them
+  for (int64_t i0 = 0; i0 < n; i0 += h->max_batch) {
+    const int B = static_cast<int>(std::min<int64_t>(h->max_batch, n - i0));
+    if (d_utf8) {
+      mark(h, K_TOKENIZE);
+      if ((rc = tokenizer_run(st, h->tok, d_utf8, d_offsets + i0, B, max_len, h->ids, nullptr, h->lens,
+                              h->num_sms))) return rc;
+      acc.launches += 1;
+    } else {
+      B2_CUDA_OK(cudaMemcpyAsync(h->ids, d_ids_in + i0 * max_len, size_t(B) * max_len * 4,
+                                 cudaMemcpyDeviceToDevice, st));
+      if ((rc = mask_to_lens(st, d_mask_in + i0 * max_len, h->lens, B, max_len))) return rc;
+      acc.launches += 1;
+    }
+    sum_lens_kernel<<<1, 256, 0, st>>>(h->lens, B, h->d_tokens);
+    acc.launches += 1;
+    int32_t* lab = d_labels ? d_labels + i0 : reinterpret_cast<int32_t*>(h->mask);  // scratch
+    if ((rc = forward_batch(h, B, max_len, topk, d_top_idx + i0 * topk, d_top_score + i0 * topk, lab,
+                            d_logits ? d_logits + i0 * C : nullptr, &acc.launches))) return rc;
+    if ((rc = flush_profile(h, &acc))) return rc;
+    ++batches;
+  }
+  if (d_hist) {
+    hist_to_i64_kernel<<<(C + 255) / 256, 256, 0, st>>>(h->hist, d_hist, C);
+    acc.launches += 1;
+  }
+  B2_CUDA_OK(cudaEventRecord(h->ev_end, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  B2_CUDA_OK(cudaGetLastError());
+  float ms = 0.f;
+  B2_CUDA_OK(cudaEventElapsedTime(&ms, h->ev_begin, h->ev_end));
+  int64_t tokens = 0;
+  B2_CUDA_OK(cudaMemcpy(&tokens, h->d_tokens, 8, cudaMemcpyDeviceToHost));
+  fill_metrics(metrics, h, acc, n, tokens, n * max_len, batches, h2d, d2h, ms);
+  return B2_OK;
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace
+}  // namespace b2
+
+// ================================================================================================
+// exported C ABI
+// ================================================================================================
+extern "C" {
+
+const char* b2_last_error(void) { return b2::last_error(); }
+
+int32_t b2_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int b2_get_device_info(int32_t device, b2_device_info* out) {
+  if (!out) { set_last_error("b2_get_device_info: out is NULL"); return B2_ERR_ARG; }
+  cudaDeviceProp p;
+  B2_CUDA_OK(cudaGetDeviceProperties(&p, device));
+  memset(out, 0, sizeof(*out));
+  strncpy(out->name, p.name, sizeof(out->name) - 1);
+  out->total_memory_bytes = static_cast<int64_t>(p.totalGlobalMem);
+  out->sm_count = p.multiProcessorCount;
+  out->cc_major = p.major;
+  out->cc_minor = p.minor;
+  out->l2_bytes = p.l2CacheSize;
+  return B2_OK;
+}
+
+int b2_create(const b2_config* cfg, b2_handle** out) {
+  if (!cfg || !out || cfg->struct_size < static_cast<int32_t>(sizeof(b2_config))) {
+    set_last_error("b2_create: config is NULL or has the wrong struct_size");
+    return B2_ERR_ARG;
+  }
+  *out = nullptr;
+  const int ndev = b2_device_count();
+  if (ndev <= 0) {
+    set_last_error("No CUDA device detected (cudaGetDeviceCount returned 0).");
+    return B2_ERR_CUDA;
+  }
+  if (cfg->device < 0 || cfg->device >= ndev) {
+    set_last_error("b2_create: device %d is outside [0, %d)", cfg->device, ndev);
+    return B2_ERR_ARG;
+  }
+  if (cfg->vocab_path && !cfg->unicode_path) {
+    set_last_error("b2_create: vocab_path needs unicode_path");
+    return B2_ERR_ARG;
+  }
+  DeviceGuard guard(cfg->device);
+  cudaDeviceProp prop;
+  B2_CUDA_OK(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major != 10) {
+    set_last_error("device %d is sm_%d%d; this library holds sm_100a code only", cfg->device,
+                   prop.major, prop.minor);
+    return B2_ERR_CUDA;
+  }
+  b2_handle* h = new b2_handle();
+  h->device = cfg->device;
+  h->num_sms = prop.multiProcessorCount;
+  h->max_batch = cfg->max_batch > 0 ? cfg->max_batch : 1024;
+  h->max_len = cfg->max_len > 0 ? cfg->max_len : 128;
+  int rc = B2_OK;
+  do {
+    if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&h->ev_begin) != cudaSuccess || cudaEventCreate(&h->ev_end) != cudaSuccess) {
+      set_last_error("b2_create: cannot create stream / events: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = B2_ERR_CUDA;
+      break;
+    }
+    if (cfg->vocab_path) {
+      if ((rc = tokenizer_load(cfg->vocab_path, cfg->unicode_path, &h->tok, &h->tok_vocab))) break;
+      h->has_tokenizer = true;
+    }
+    if (cfg->model_path) {
+      if ((rc = load_model(h, cfg->model_path))) break;
+      if (static_cast<uint32_t>(h->max_len) > h->mh.max_positions) h->max_len = h->mh.max_positions;
+    }
+    if ((rc = alloc_activations(h))) break;
+  } while (0);
+  if (rc) {
+    b2_destroy(h);
+    return rc;
+  }
+  *out = h;
+  return B2_OK;
+}
+
+void b2_destroy(b2_handle* h) {
+  if (!h) return;
+  DeviceGuard guard(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  for (void* p : h->allocations) cudaFree(p);
+  if (h->has_tokenizer) tokenizer_free(&h->tok);
+  if (h->st_text) cudaFree(h->st_text);
+  if (h->st_off) cudaFree(h->st_off);
+  if (h->st_out) cudaFree(h->st_out);
+  for (cudaEvent_t e : h->events) cudaEventDestroy(e);
+  if (h->ev_begin) cudaEventDestroy(h->ev_begin);
+  if (h->ev_end) cudaEventDestroy(h->ev_end);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+int b2_get_model_info(b2_handle* h, b2_model_info* out) {
+  if (!h || !out) { set_last_error("b2_get_model_info: NULL argument"); return B2_ERR_ARG; }
+  memset(out, 0, sizeof(*out));
+  if (h->has_model) {
+    out->hidden = h->mh.hidden; out->layers = h->mh.layers; out->heads = h->mh.heads;
+    out->intermediate = h->mh.intermediate; out->vocab_size = h->mh.vocab_size;
+    out->max_positions = h->mh.max_positions; out->num_labels = h->mh.num_labels;
+  }
+  out->tokenizer_vocab_size = h->tok_vocab;
+  out->max_batch = h->max_batch; out->max_len = h->max_len; out->device = h->device;
+  out->sm_count = h->num_sms;
+  out->weight_bytes = h->weight_bytes; out->activation_bytes = h->activation_bytes;
+  return B2_OK;
+}
+
+int b2_set_profiling(b2_handle* h, int32_t on) {
+  if (!h) { set_last_error("b2_set_profiling: NULL handle"); return B2_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  h->profiling = on != 0;
+  h->n_events = 0;
+  return B2_OK;
+}
+
+int b2_tokenize_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offsets, int64_t n,
+                       int64_t n_bytes, int32_t max_len, int32_t* d_ids, uint8_t* d_mask,
+                       b2_metrics* metrics) {
+  (void)n_bytes;
+  if (!h) { set_last_error("b2_tokenize_device: NULL handle"); return B2_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  if (!h->has_tokenizer) {
+    set_last_error("this handle was created without a tokenizer (b2_config.vocab_path was NULL)");
+    return B2_ERR_ARG;
+  }
+  if (max_len < 2) { set_last_error("tokenize: max_len must be >= 2"); return B2_ERR_ARG; }
+  if (n < 0 || n > 0x7fffffff || (n > 0 && !d_ids)) {
+    set_last_error("tokenize: n out of range or ids is NULL");
+    return B2_ERR_ARG;
+  }
+  KindAcc acc;
+  B2_CUDA_OK(cudaEventRecord(h->ev_begin, h->stream));
+  mark(h, K_TOKENIZE);
+  int rc = tokenizer_run(h->stream, h->tok, d_utf8, d_offsets, static_cast<int>(n), max_len, d_ids,
+                         d_mask, nullptr, h->num_sms);
+  if (rc) return rc;
+  acc.launches = n > 0 ? 1 : 0;
+  if ((rc = flush_profile(h, &acc))) return rc;
+  B2_CUDA_OK(cudaEventRecord(h->ev_end, h->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(h->stream));
+  B2_CUDA_OK(cudaGetLastError());
+  float ms = 0.f;
+  B2_CUDA_OK(cudaEventElapsedTime(&ms, h->ev_begin, h->ev_end));
+  fill_metrics(metrics, h, acc, n, 0, n * max_len, 1, 0, 0, ms);
+  return B2_OK;
+}
+
+static int stage_text(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                      int64_t* n_bytes) {
+  if (n < 0 || n > 0x7fffffff || (n > 0 && (!utf8 && offsets[n] > 0)) || !offsets) {
+    set_last_error("text input: n out of range or NULL utf8 / offsets");
+    return B2_ERR_ARG;
+  }
+  const int64_t bytes = offsets[n];
+  if (offsets[0] != 0 || bytes < 0) {
+    set_last_error("text input: offsets must start at 0 and be non-decreasing");
+    return B2_ERR_ARG;
+  }
+  int rc;
+  if ((rc = grow(reinterpret_cast<void**>(&h->st_text), &h->st_text_cap, bytes + 16))) return rc;
+  if ((rc = grow(reinterpret_cast<void**>(&h->st_off), &h->st_off_cap, (n + 1) * 8))) return rc;
+  if (bytes) B2_CUDA_OK(cudaMemcpyAsync(h->st_text, utf8, bytes, cudaMemcpyHostToDevice, h->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(h->st_off, offsets, (n + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+  *n_bytes = bytes;
+  return B2_OK;
+}
+
+int b2_tokenize(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n, int32_t max_len,
+                int32_t* ids, uint8_t* mask, b2_metrics* metrics) {
+  if (!h) { set_last_error("b2_tokenize: NULL handle"); return B2_ERR_ARG; }
+  int64_t bytes = 0;
+  size_t out_ids = 0, out_mask = 0;
+  {
+    std::lock_guard<std::mutex> lock(h->mu);
+    DeviceGuard guard(h->device);
+    if (max_len < 2) { set_last_error("tokenize: max_len must be >= 2"); return B2_ERR_ARG; }
+    if (n > 0 && !ids) { set_last_error("tokenize: ids is NULL"); return B2_ERR_ARG; }
+    int rc;
+    if ((rc = stage_text(h, utf8, offsets, n, &bytes))) return rc;
+    out_ids = size_t(n) * max_len * 4;
+    out_mask = mask ? size_t(n) * max_len : 0;
+    if ((rc = grow(&h->st_out, &h->st_out_cap, out_ids + out_mask + 64))) return rc;
+  }
+  int32_t* d_ids = static_cast<int32_t*>(h->st_out);
+  uint8_t* d_mask = mask ? reinterpret_cast<uint8_t*>(h->st_out) + out_ids : nullptr;
+  b2_metrics local;
+  memset(&local, 0, sizeof(local));
+  local.struct_size = sizeof(local);
+  int rc = b2_tokenize_device(h, h->st_text, h->st_off, n, bytes, max_len, d_ids, d_mask, &local);
+  if (rc) return rc;
+  {
+    std::lock_guard<std::mutex> lock(h->mu);
+    DeviceGuard guard(h->device);
+    if (out_ids) B2_CUDA_OK(cudaMemcpy(ids, d_ids, out_ids, cudaMemcpyDeviceToHost));
+    if (out_mask) B2_CUDA_OK(cudaMemcpy(mask, d_mask, out_mask, cudaMemcpyDeviceToHost));
+  }
+  local.h2d_bytes = bytes + (n + 1) * 8;
+  local.d2h_bytes = out_ids + out_mask;
+  if (metrics && metrics->struct_size > 0) {
+    const int32_t keep = metrics->struct_size;
+    memcpy(metrics, &local, std::min<size_t>(sizeof(local), keep));
+    metrics->struct_size = keep;
+  }
+  return B2_OK;
+}
+
+int b2_classify_text_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offsets, int64_t n,
+                            int64_t n_bytes, int32_t max_len, int32_t topk, int32_t* d_top_idx,
+                            float* d_top_score, int32_t* d_labels, int64_t* d_histogram,
+                            float* d_logits, b2_metrics* metrics) {
+  (void)n_bytes;
+  if (!h) { set_last_error("b2_classify_text_device: NULL handle"); return B2_ERR_ARG; }
+  if (n > 0 && (!d_utf8 || !d_offsets)) {
+    set_last_error("classify: NULL text / offsets");
+    return B2_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  return classify_device(h, d_utf8, d_offsets, nullptr, nullptr, n, max_len, topk, d_top_idx,
+                         d_top_score, d_labels, d_histogram, d_logits, metrics, 0, 0);
+}
+
+// outputs staged on the device in one block: top_idx | top_score | labels | hist | logits
+struct OutLayout {
+  size_t top_idx, top_score, labels, hist, logits, total;
+};
+static OutLayout out_layout(int64_t n, int topk, int C, bool want_logits) {
+  OutLayout L;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~size_t(255); return at; };
+  L.top_idx = take(size_t(n) * topk * 4);
+  L.top_score = take(size_t(n) * topk * 4);
+  L.labels = take(size_t(n) * 4);
+  L.hist = take(size_t(C) * 8);
+  L.logits = take(want_logits ? size_t(n) * C * 4 : 0);
+  L.total = o + 256;
+  return L;
+}
+
+static int classify_host(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, const int32_t* ids,
+                         const uint8_t* mask, int64_t n, int32_t max_len, int32_t topk,
+                         int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
+                         float* logits, b2_metrics* metrics) {
+  if (!h) { set_last_error("classify: NULL handle"); return B2_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  int rc;
+  if ((rc = check_len(h, max_len, true))) return rc;
+  const int C = h->mh.num_labels;
+  if (topk < 1 || topk > C) {
+    set_last_error("topk %d is outside [1, num_labels = %d]", topk, C);
+    return B2_ERR_ARG;
+  }
+  if (n < 0 || n > 0x7fffffff || (n > 0 && (!top_idx || !top_score))) {
+    set_last_error("classify: n out of range or top_idx / top_score is NULL");
+    return B2_ERR_ARG;
+  }
+  int64_t h2d = 0;
+  const uint8_t* d_text = nullptr;
+  const int64_t* d_off = nullptr;
+  const int32_t* d_ids = nullptr;
+  const uint8_t* d_mask = nullptr;
+  if (utf8 || offsets) {
+    int64_t bytes = 0;
+    if ((rc = stage_text(h, utf8, offsets, n, &bytes))) return rc;
+    d_text = h->st_text; d_off = h->st_off;
+    h2d = bytes + (n + 1) * 8;
+  } else {
+    if (n > 0 && (!ids || !mask)) { set_last_error("classify: NULL ids / mask"); return B2_ERR_ARG; }
+    const size_t ib = size_t(n) * max_len * 4, mb = size_t(n) * max_len;
+    if ((rc = grow(reinterpret_cast<void**>(&h->st_text), &h->st_text_cap, ib + mb + 64))) return rc;
+    if (ib) B2_CUDA_OK(cudaMemcpyAsync(h->st_text, ids, ib, cudaMemcpyHostToDevice, h->stream));
+    if (mb) B2_CUDA_OK(cudaMemcpyAsync(h->st_text + ib, mask, mb, cudaMemcpyHostToDevice, h->stream));
+    d_ids = reinterpret_cast<const int32_t*>(h->st_text);
+    d_mask = h->st_text + ib;
+    h2d = ib + mb;
+  }
+  const OutLayout L = out_layout(n, topk, C, logits != nullptr);
+  if ((rc = grow(&h->st_out, &h->st_out_cap, L.total))) return rc;
+  uint8_t* ob = static_cast<uint8_t*>(h->st_out);
+  int64_t d2h = size_t(n) * topk * 8 + (labels ? n * 4 : 0) + (histogram ? C * 8 : 0) +
+                (logits ? size_t(n) * C * 4 : 0);
+  rc = classify_device(h, d_text, d_off, d_ids, d_mask, n, max_len, topk,
+                       reinterpret_cast<int32_t*>(ob + L.top_idx),
+                       reinterpret_cast<float*>(ob + L.top_score),
+                       reinterpret_cast<int32_t*>(ob + L.labels),
+                       reinterpret_cast<int64_t*>(ob + L.hist),
+                       logits ? reinterpret_cast<float*>(ob + L.logits) : nullptr, metrics, h2d, d2h);
+  if (rc) return rc;
+  if (n > 0) {
+    B2_CUDA_OK(cudaMemcpy(top_idx, ob + L.top_idx, size_t(n) * topk * 4, cudaMemcpyDeviceToHost));
+    B2_CUDA_OK(cudaMemcpy(top_score, ob + L.top_score, size_t(n) * topk * 4, cudaMemcpyDeviceToHost));
+    if (labels) B2_CUDA_OK(cudaMemcpy(labels, ob + L.labels, size_t(n) * 4, cudaMemcpyDeviceToHost));
+    if (logits) B2_CUDA_OK(cudaMemcpy(logits, ob + L.logits, size_t(n) * C * 4, cudaMemcpyDeviceToHost));
+  }
+  if (histogram) B2_CUDA_OK(cudaMemcpy(histogram, ob + L.hist, size_t(C) * 8, cudaMemcpyDeviceToHost));
+  return B2_OK;
+}
+
+int b2_classify_text(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                     int32_t max_len, int32_t topk, int32_t* top_idx, float* top_score,
+                     int32_t* labels, int64_t* histogram, float* logits, b2_metrics* metrics) {
+  if (!offsets) { set_last_error("b2_classify_text: offsets is NULL"); return B2_ERR_ARG; }
+  static const uint8_t empty = 0;
+  return classify_host(h, utf8 ? utf8 : &empty, offsets, nullptr, nullptr, n, max_len, topk, top_idx,
+                       top_score, labels, histogram, logits, metrics);
+}
+
+int b2_classify_ids(b2_handle* h, const int32_t* ids, const uint8_t* mask, int64_t n, int32_t max_len,
+                    int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels,
+                    int64_t* histogram, float* logits, b2_metrics* metrics) {
+  return classify_host(h, nullptr, nullptr, ids, mask, n, max_len, topk, top_idx, top_score, labels,
+                       histogram, logits, metrics);
+}
+
+int b2_chunk_count(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                   int64_t* counts) {
+  if (!h || !offsets || (n > 0 && !counts)) { set_last_error("b2_chunk_count: NULL argument"); return B2_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  static const uint8_t empty = 0;
+  int64_t bytes = 0;
+  int rc;
+  if ((rc = stage_text(h, utf8 ? utf8 : &empty, offsets, n, &bytes))) return rc;
+  if ((rc = grow(&h->st_out, &h->st_out_cap, size_t(n) * 8 + 64))) return rc;
+  if ((rc = chunk_count(h->stream, h->st_text, h->st_off, static_cast<int>(n),
+                        static_cast<int64_t*>(h->st_out)))) return rc;
+  B2_CUDA_OK(cudaStreamSynchronize(h->stream));
+  if (n) B2_CUDA_OK(cudaMemcpy(counts, h->st_out, size_t(n) * 8, cudaMemcpyDeviceToHost));
+  return B2_OK;
+}
+
+int b2_chunk_bounds(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                    int64_t chunk_size, const int64_t* chunk_base, int64_t n_chunks, int64_t* bounds) {
+  if (!h || !offsets || (n > 0 && !chunk_base) || (n_chunks > 0 && !bounds) || chunk_size <= 0) {
+    set_last_error("b2_chunk_bounds: NULL argument or chunk_size <= 0");
+    return B2_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  static const uint8_t empty = 0;
+  int64_t bytes = 0;
+  int rc;
+  if ((rc = stage_text(h, utf8 ? utf8 : &empty, offsets, n, &bytes))) return rc;
+  const size_t base_bytes = (size_t(n) * 8 + 255) & ~size_t(255);
+  if ((rc = grow(&h->st_out, &h->st_out_cap, base_bytes + size_t(n_chunks) * 8 + 64))) return rc;
+  int64_t* d_base = static_cast<int64_t*>(h->st_out);
+  int64_t* d_bounds = reinterpret_cast<int64_t*>(static_cast<uint8_t*>(h->st_out) + base_bytes);
+  if (n) B2_CUDA_OK(cudaMemcpyAsync(d_base, chunk_base, size_t(n) * 8, cudaMemcpyHostToDevice, h->stream));
+  if ((rc = chunk_bounds(h->stream, h->st_text, h->st_off, static_cast<int>(n), chunk_size, d_base,
+                         d_bounds))) return rc;
+  B2_CUDA_OK(cudaStreamSynchronize(h->stream));
+  if (n_chunks) B2_CUDA_OK(cudaMemcpy(bounds, d_bounds, size_t(n_chunks) * 8, cudaMemcpyDeviceToHost));
+  return B2_OK;
+}
+
+}  // extern "C"

@@ -9,6 +9,8 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 
+#include "b2_classify.h"  // B2_OK / B2_ERR_* codes
+
 namespace b2 {
 
 // ----------------------------------------------------------------------------------------------
@@ -27,14 +29,6 @@ const char* last_error();
     }                                                                                      \
   } while (0)
 
-enum {
-  B2_OK = 0,
-  B2_ERR_ARG = 1,
-  B2_ERR_CUDA = 2,
-  B2_ERR_IO = 3,
-  B2_ERR_FORMAT = 4,
-  B2_ERR_LIMIT = 5,
-};
 
 // ----------------------------------------------------------------------------------------------
 // device helpers

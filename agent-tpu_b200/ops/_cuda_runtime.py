@@ -1,0 +1,392 @@
+"""B200 accelerator runtime for the ops: replaces the reference's ops/_tpu_runtime.py.
+
+Same shape as the reference module (ops/_tpu_runtime.py:15-63):
+  * `get_model_path(requested)`  — precedence: payload, environment, built-in default;
+  * `get_cuda_handle(model_path)` — process-wide single-slot cache keyed on the path, lazy import of
+    the native dependency so the agent starts without it, device probe, file-existence check, load;
+  * a frozen handle dataclass `(interpreter, input_details, output_details, model_path)`.
+
+Underneath, the "interpreter" is `Engine`, a ctypes binding of libb2classify.so
+(include/b2_classify.h). There is no CPU fallback: if the library or a CUDA device is missing the
+calls raise, and the op's own `except` turns that into the reference's error envelope
+(ops/map_classify_tpu.py:84-90).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+_PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG_DIR, "csrc", "libb2classify.so")
+UNICODE_TABLE_PATH = os.path.join(_PKG_DIR, "data", "bert_unicode.bin")
+DEFAULT_MODEL_PATH = "/models/model_b200.b2m"
+
+# Lazy, process-wide cache (single slot, like ops/_tpu_runtime.py:9-12)
+_ENGINE = None
+_INPUT_DETAILS = None
+_OUTPUT_DETAILS = None
+_MODEL_PATH = None
+_CACHE_KEY = None
+_LOCK = threading.Lock()  # the reference's cache is unlocked; creation is locked here
+_LIB = None
+
+
+class B2Error(RuntimeError):
+    """A non-zero return code from libb2classify.so."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(message)
+        self.code = code
+
+
+class _Config(C.Structure):
+    _fields_ = [("struct_size", C.c_int32), ("device", C.c_int32), ("model_path", C.c_char_p),
+                ("vocab_path", C.c_char_p), ("unicode_path", C.c_char_p), ("max_batch", C.c_int32),
+                ("max_len", C.c_int32)]
+
+
+class ModelInfo(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("hidden", "layers", "heads", "intermediate", "vocab_size",
+                                         "max_positions", "num_labels", "tokenizer_vocab_size",
+                                         "max_batch", "max_len", "device", "sm_count")] + \
+               [("weight_bytes", C.c_int64), ("activation_bytes", C.c_int64)]
+
+
+_METRIC_KINDS = ("tokenize", "embed", "gemm_qkv", "attention", "gemm_attn_out", "layernorm", "gemm_ffn1",
+                 "gemm_ffn2", "pooler", "head")
+
+
+class Metrics(C.Structure):
+    _fields_ = [("struct_size", C.c_int32), ("profiled", C.c_int32)] + \
+               [(n, C.c_int64) for n in ("items", "tokens", "padded_tokens", "batches", "kernel_launches",
+                                         "h2d_bytes", "d2h_bytes")] + \
+               [("gpu_ms_total", C.c_double)] + [("ms_" + k, C.c_double) for k in _METRIC_KINDS] + \
+               [("n_" + k, C.c_int64) for k in _METRIC_KINDS]
+
+    def as_dict(self) -> dict:
+        d = {n: int(getattr(self, n)) for n in ("items", "tokens", "padded_tokens", "batches",
+                                                 "kernel_launches", "h2d_bytes", "d2h_bytes")}
+        d["gpu_ms_total"] = float(self.gpu_ms_total)
+        if self.profiled:
+            d["kernels"] = {k: {"ms": float(getattr(self, "ms_" + k)), "launches": int(getattr(self, "n_" + k))}
+                            for k in _METRIC_KINDS}
+        return d
+
+
+class DeviceInfo(C.Structure):
+    _fields_ = [("name", C.c_char * 128), ("total_memory_bytes", C.c_int64), ("sm_count", C.c_int32),
+                ("cc_major", C.c_int32), ("cc_minor", C.c_int32), ("l2_bytes", C.c_int32)]
+
+
+def load_library():
+    """dlopen libb2classify.so and declare its prototypes. Raises OSError if it is not built."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise OSError(f"libb2classify.so is not built: {LIB_PATH} (run `python -c 'import __graft_entry__ "
+                      f"as g; g.build()'` or `make -C agent-tpu_b200/csrc`)")
+    lib = C.CDLL(LIB_PATH)
+    P, I32, I64 = C.c_void_p, C.c_int32, C.c_int64
+    lib.b2_last_error.restype = C.c_char_p
+    lib.b2_last_error.argtypes = []
+    lib.b2_device_count.restype = I32
+    lib.b2_device_count.argtypes = []
+    lib.b2_get_device_info.argtypes = [I32, C.POINTER(DeviceInfo)]
+    lib.b2_create.argtypes = [C.POINTER(_Config), C.POINTER(P)]
+    lib.b2_destroy.argtypes = [P]
+    lib.b2_destroy.restype = None
+    lib.b2_get_model_info.argtypes = [P, C.POINTER(ModelInfo)]
+    lib.b2_set_profiling.argtypes = [P, I32]
+    lib.b2_tokenize.argtypes = [P, P, P, I64, I32, P, P, C.POINTER(Metrics)]
+    lib.b2_tokenize_device.argtypes = [P, P, P, I64, I64, I32, P, P, C.POINTER(Metrics)]
+    lib.b2_classify_text.argtypes = [P, P, P, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
+    lib.b2_classify_text_device.argtypes = [P, P, P, I64, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
+    lib.b2_classify_ids.argtypes = [P, P, P, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
+    lib.b2_chunk_count.argtypes = [P, P, P, I64, P]
+    lib.b2_chunk_bounds.argtypes = [P, P, P, I64, I64, P, I64, P]
+    for name in ("b2_get_device_info", "b2_create", "b2_get_model_info", "b2_set_profiling", "b2_tokenize",
+                 "b2_tokenize_device", "b2_classify_text", "b2_classify_text_device", "b2_classify_ids",
+                 "b2_chunk_count", "b2_chunk_bounds"):
+        getattr(lib, name).restype = C.c_int
+    _LIB = lib
+    return lib
+
+
+def _check(lib, rc: int) -> None:
+    if rc != 0:
+        msg = lib.b2_last_error()
+        raise B2Error(rc, (msg or b"").decode("utf-8", "replace") or f"libb2classify error {rc}")
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def pack_items(items: Sequence[str]) -> Tuple[np.ndarray, np.ndarray]:
+    """Concatenate items as UTF-8 (uint8 array) and int64 offsets[n+1] — the C ABI's text layout.
+
+    The boundary of Python at 1M items is one join and one cumsum, not a per-item ctypes call
+    (SURVEY.md §7.2 "Python at the boundary dominates")."""
+    enc = [s.encode("utf-8", "surrogatepass") for s in items]
+    offsets = np.zeros(len(enc) + 1, dtype=np.int64)
+    if enc:
+        np.cumsum(np.fromiter((len(b) for b in enc), dtype=np.int64, count=len(enc)), out=offsets[1:])
+    blob = np.frombuffer(b"".join(enc), dtype=np.uint8) if enc else np.zeros(0, dtype=np.uint8)
+    return blob, offsets
+
+
+class Engine:
+    """One model + tokenizer resident on one CUDA device (the reference's `interpreter` slot)."""
+
+    def __init__(self, model_path: Optional[str], vocab_path: Optional[str], device: int = 0,
+                 max_batch: int = 1024, max_len: int = 128):
+        self._lib = load_library()
+        self._h = C.c_void_p()
+        cfg = _Config(C.sizeof(_Config), int(device),
+                      model_path.encode() if model_path else None,
+                      vocab_path.encode() if vocab_path else None,
+                      UNICODE_TABLE_PATH.encode() if vocab_path else None,
+                      int(max_batch), int(max_len))
+        _check(self._lib, self._lib.b2_create(C.byref(cfg), C.byref(self._h)))
+        self.info = ModelInfo()
+        _check(self._lib, self._lib.b2_get_model_info(self._h, C.byref(self.info)))
+        self.model_path = model_path
+        self.vocab_path = vocab_path
+        self.device = int(device)
+
+    # -- life cycle --------------------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.b2_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self) -> C.c_void_p:
+        return self._h
+
+    def set_profiling(self, on: bool) -> None:
+        _check(self._lib, self._lib.b2_set_profiling(self._h, 1 if on else 0))
+
+    # -- tokenizer ---------------------------------------------------------------------------
+    def tokenize_packed(self, blob: np.ndarray, offsets: np.ndarray, max_len: int,
+                        want_mask: bool = True) -> Tuple[np.ndarray, Optional[np.ndarray], dict]:
+        n = len(offsets) - 1
+        ids = np.empty((n, max_len), dtype=np.int32)
+        mask = np.empty((n, max_len), dtype=np.uint8) if want_mask else None
+        m = Metrics(struct_size=C.sizeof(Metrics))
+        _check(self._lib, self._lib.b2_tokenize(self._h, _ptr(blob), _ptr(offsets), n, int(max_len),
+                                                _ptr(ids), _ptr(mask), C.byref(m)))
+        return ids, mask, m.as_dict()
+
+    def tokenize(self, items: Sequence[str], max_len: int = 128):
+        blob, offsets = pack_items(items)
+        return self.tokenize_packed(blob, offsets, max_len)
+
+    # -- classification ----------------------------------------------------------------------
+    def _outputs(self, n: int, topk: int, want_logits: bool):
+        Cn = int(self.info.num_labels)
+        return (np.empty((n, topk), dtype=np.int32), np.empty((n, topk), dtype=np.float32),
+                np.empty(n, dtype=np.int32), np.zeros(Cn, dtype=np.int64),
+                np.empty((n, Cn), dtype=np.float32) if want_logits else None)
+
+    def classify_packed(self, blob: np.ndarray, offsets: np.ndarray, max_len: int = 128, topk: int = 5,
+                        want_logits: bool = False) -> dict:
+        n = len(offsets) - 1
+        top_idx, top_score, labels, hist, logits = self._outputs(n, topk, want_logits)
+        m = Metrics(struct_size=C.sizeof(Metrics))
+        _check(self._lib, self._lib.b2_classify_text(self._h, _ptr(blob), _ptr(offsets), n, int(max_len),
+                                                     int(topk), _ptr(top_idx), _ptr(top_score), _ptr(labels),
+                                                     _ptr(hist), _ptr(logits), C.byref(m)))
+        return {"top_idx": top_idx, "top_score": top_score, "labels": labels, "histogram": hist,
+                "logits": logits, "metrics": m.as_dict()}
+
+    def classify(self, items: Sequence[str], max_len: int = 128, topk: int = 5,
+                 want_logits: bool = False) -> dict:
+        blob, offsets = pack_items(items)
+        return self.classify_packed(blob, offsets, max_len, topk, want_logits)
+
+    def classify_ids(self, ids: np.ndarray, mask: np.ndarray, topk: int = 5, want_logits: bool = False) -> dict:
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        mask = np.ascontiguousarray(mask, dtype=np.uint8)
+        if ids.ndim != 2 or mask.shape != ids.shape:
+            raise ValueError("ids and mask must be [n, max_len] arrays of the same shape")
+        n, max_len = ids.shape
+        top_idx, top_score, labels, hist, logits = self._outputs(n, topk, want_logits)
+        m = Metrics(struct_size=C.sizeof(Metrics))
+        _check(self._lib, self._lib.b2_classify_ids(self._h, _ptr(ids), _ptr(mask), n, int(max_len), int(topk),
+                                                    _ptr(top_idx), _ptr(top_score), _ptr(labels), _ptr(hist),
+                                                    _ptr(logits), C.byref(m)))
+        return {"top_idx": top_idx, "top_score": top_score, "labels": labels, "histogram": hist,
+                "logits": logits, "metrics": m.as_dict()}
+
+    def classify_device(self, d_text: int, d_offsets: int, n: int, n_bytes: int, max_len: int, topk: int,
+                        d_top_idx: int, d_top_score: int, d_labels: int, d_hist: int, d_logits: int = 0) -> dict:
+        """Everything already resident in this device's HBM (raw device addresses)."""
+        m = Metrics(struct_size=C.sizeof(Metrics))
+        _check(self._lib, self._lib.b2_classify_text_device(
+            self._h, C.c_void_p(d_text), C.c_void_p(d_offsets), int(n), int(n_bytes), int(max_len), int(topk),
+            C.c_void_p(d_top_idx), C.c_void_p(d_top_score), C.c_void_p(d_labels or None),
+            C.c_void_p(d_hist or None), C.c_void_p(d_logits or None), C.byref(m)))
+        return m.as_dict()
+
+    def tokenize_device(self, d_text: int, d_offsets: int, n: int, n_bytes: int, max_len: int,
+                        d_ids: int, d_mask: int = 0) -> dict:
+        m = Metrics(struct_size=C.sizeof(Metrics))
+        _check(self._lib, self._lib.b2_tokenize_device(
+            self._h, C.c_void_p(d_text), C.c_void_p(d_offsets), int(n), int(n_bytes), int(max_len),
+            C.c_void_p(d_ids), C.c_void_p(d_mask or None), C.byref(m)))
+        return m.as_dict()
+
+    # -- fixed-width chunking (map_tokenize) -------------------------------------------------
+    def chunk_counts(self, blob: np.ndarray, offsets: np.ndarray) -> np.ndarray:
+        n = len(offsets) - 1
+        counts = np.zeros(n, dtype=np.int64)
+        _check(self._lib, self._lib.b2_chunk_count(self._h, _ptr(blob), _ptr(offsets), n, _ptr(counts)))
+        return counts
+
+    def chunk_bounds(self, blob: np.ndarray, offsets: np.ndarray, chunk_size: int,
+                     chunk_base: np.ndarray, n_chunks: int) -> np.ndarray:
+        n = len(offsets) - 1
+        bounds = np.zeros(max(n_chunks, 1), dtype=np.int64)
+        base = np.ascontiguousarray(chunk_base, dtype=np.int64)
+        _check(self._lib, self._lib.b2_chunk_bounds(self._h, _ptr(blob), _ptr(offsets), n, int(chunk_size),
+                                                    _ptr(base), int(n_chunks), _ptr(bounds)))
+        return bounds[:n_chunks]
+
+
+@dataclass(frozen=True)
+class CUDAHandle:
+    """Counterpart of TPUHandle (ops/_tpu_runtime.py:15-20)."""
+    interpreter: object      # Engine
+    input_details: object    # [{"index", "shape", "dtype"}] — one pre-tokenised row, like the v0 contract
+    output_details: object   # [{"index", "shape", "dtype"}] — one row of class scores
+    model_path: str
+
+
+def get_model_path(requested: Optional[str] = None) -> str:
+    """Payload value, else $CUDA_MODEL_PATH, else $TPU_MODEL_PATH (kept so an existing deployment's
+    environment still works), else the default — same precedence as ops/_tpu_runtime.py:23-31."""
+    return (
+        requested
+        or os.environ.get("CUDA_MODEL_PATH")
+        or os.environ.get("TPU_MODEL_PATH")
+        or DEFAULT_MODEL_PATH
+    )
+
+
+def get_vocab_path(model_path: str, requested: Optional[str] = None) -> str:
+    """vocab.txt: payload value, else $CUDA_VOCAB_PATH, else `vocab.txt` beside the model file."""
+    return (
+        requested
+        or os.environ.get("CUDA_VOCAB_PATH")
+        or os.path.join(os.path.dirname(os.path.abspath(model_path)), "vocab.txt")
+    )
+
+
+def device_count() -> int:
+    return int(load_library().b2_device_count())
+
+
+def device_infos() -> List[dict]:
+    """Per-device facts for worker_sizing (replaces the nvidia-smi subprocess)."""
+    lib = load_library()
+    out = []
+    for i in range(int(lib.b2_device_count())):
+        d = DeviceInfo()
+        _check(lib, lib.b2_get_device_info(i, C.byref(d)))
+        out.append({"index": i, "name": d.name.decode("utf-8", "replace"),
+                    "total_memory_bytes": int(d.total_memory_bytes), "sm_count": int(d.sm_count),
+                    "compute_capability": f"{d.cc_major}.{d.cc_minor}", "l2_bytes": int(d.l2_bytes)})
+    return out
+
+
+def _local_device() -> int:
+    """One process per GPU under torchrun: LOCAL_RANK picks the device; otherwise $B2_DEVICE or 0."""
+    for var in ("B2_DEVICE", "LOCAL_RANK"):
+        v = os.environ.get(var)
+        if v is not None and v.strip().lstrip("-").isdigit():
+            return int(v)
+    return 0
+
+
+def get_cuda_handle(model_path: str, vocab_path: Optional[str] = None, max_len: int = 128,
+                    max_batch: int = 1024) -> CUDAHandle:
+    """Create/reuse the engine for `model_path` (ops/_tpu_runtime.py:34-63).
+
+    Imports (dlopens) the native library only when needed, so the agent can start without it."""
+    global _ENGINE, _INPUT_DETAILS, _OUTPUT_DETAILS, _MODEL_PATH, _CACHE_KEY
+
+    vocab = get_vocab_path(model_path, vocab_path)
+    key = (model_path, vocab, int(max_len), int(max_batch))
+    with _LOCK:
+        # Reuse if the same model is already loaded
+        if _ENGINE is not None and _CACHE_KEY is not None and _CACHE_KEY[:2] == key[:2] \
+                and _CACHE_KEY[2] >= key[2] and _CACHE_KEY[3] >= key[3]:
+            return CUDAHandle(_ENGINE, _INPUT_DETAILS, _OUTPUT_DETAILS, _MODEL_PATH)
+
+        lib = load_library()
+        if lib.b2_device_count() <= 0:
+            raise RuntimeError("No CUDA device detected (b2_device_count() returned 0).")
+        if not os.path.exists(model_path):
+            raise FileNotFoundError(f"CUDA model not found: {model_path}")
+        if not os.path.exists(vocab):
+            raise FileNotFoundError(f"CUDA tokenizer vocabulary not found: {vocab}")
+
+        if _ENGINE is not None:
+            _ENGINE.close()
+            _ENGINE = None
+        eng = Engine(model_path, vocab, device=_local_device(), max_batch=max_batch, max_len=max_len)
+        _ENGINE = eng
+        _INPUT_DETAILS = [{"index": 0, "shape": (1, int(eng.info.max_len)), "dtype": np.int32}]
+        _OUTPUT_DETAILS = [{"index": 0, "shape": (1, int(eng.info.num_labels)), "dtype": np.float32}]
+        _MODEL_PATH = model_path
+        _CACHE_KEY = (model_path, vocab, int(eng.info.max_len), int(eng.info.max_batch))
+        return CUDAHandle(_ENGINE, _INPUT_DETAILS, _OUTPUT_DETAILS, _MODEL_PATH)
+
+
+# A tokenizer-only engine for map_tokenize (no model needed): cached per vocabulary path.
+_TOK_ENGINE = None
+_TOK_KEY = None
+
+
+def get_tokenizer_engine(vocab_path: Optional[str] = None, max_len: int = 512) -> Engine:
+    global _TOK_ENGINE, _TOK_KEY
+    with _LOCK:
+        if _ENGINE is not None and vocab_path in (None, _ENGINE.vocab_path) and _ENGINE.info.max_len >= max_len:
+            return _ENGINE
+        key = (vocab_path, int(max_len))
+        if _TOK_ENGINE is not None and _TOK_KEY[0] == vocab_path and _TOK_KEY[1] >= max_len:
+            return _TOK_ENGINE
+        lib = load_library()
+        if lib.b2_device_count() <= 0:
+            raise RuntimeError("No CUDA device detected (b2_device_count() returned 0).")
+        if vocab_path is not None and not os.path.exists(vocab_path):
+            raise FileNotFoundError(f"CUDA tokenizer vocabulary not found: {vocab_path}")
+        if _TOK_ENGINE is not None:
+            _TOK_ENGINE.close()
+        _TOK_ENGINE = Engine(None, vocab_path, device=_local_device(), max_batch=1, max_len=max_len)
+        _TOK_KEY = key
+        return _TOK_ENGINE
+
+
+def reset_cache() -> None:
+    """Drop cached engines (tests)."""
+    global _ENGINE, _INPUT_DETAILS, _OUTPUT_DETAILS, _MODEL_PATH, _CACHE_KEY, _TOK_ENGINE, _TOK_KEY
+    with _LOCK:
+        for e in (_ENGINE, _TOK_ENGINE):
+            if e is not None:
+                e.close()
+        _ENGINE = _INPUT_DETAILS = _OUTPUT_DETAILS = _MODEL_PATH = _CACHE_KEY = None
+        _TOK_ENGINE = _TOK_KEY = None

@@ -1,0 +1,143 @@
+"""map_classify_tpu on B200: same registration, payload and result envelope as the reference op
+(ops/map_classify_tpu.py:31-90, ops/map_classify_tpu.CONTRACT.md), batch-capable underneath.
+
+Kept from the reference
+  * `@register_op("map_classify_tpu")`, handler `run(payload, ctx=None)`, `payload=None` tolerated;
+  * v0 keys: `input` (flat list[int], one pre-tokenised row), `model_path`, `topk` (default 5),
+    `allow_fallback` (default True); result `{op, model_path, topk:[{index, score}], elapsed_ms}`;
+  * k is clamped to [1, number of classes] (ops/map_classify_tpu.py:16);
+  * any exception becomes `{op, fallback:"cpu", reason, topk:[], elapsed_ms}` unless
+    `allow_fallback` is falsy, in which case it propagates (ops/map_classify_tpu.py:84-90). The
+    "cpu" in that envelope is the reference's wording for "the accelerator did not run"; no CPU
+    computation happens there or here.
+
+Added: `items: list[str]` (the key map_tokenize already uses,
+ops/map_tokenize.py:29) classifies a whole job: tokenised on the GPU, encoded in batches of
+`batch` (default 1024) at padded length `max_len` (default 128). The result then also carries
+`items_count`, `labels`, `label_histogram`, `metrics` and, with `return_results`, per-item `results`.
+Top-level `topk` stays (first item) so v0 consumers keep working.
+"""
+from __future__ import annotations
+
+import time
+from typing import Any, Dict, List
+
+import numpy as np
+
+from . import register_op
+from ._cuda_runtime import get_model_path, get_cuda_handle
+from . import _shard
+
+OP_NAME = "map_classify_tpu"
+PAD_ID = 0  # [PAD] in BERT vocabularies; a v0 `input` row is masked where it equals this id
+
+
+def _clamp_k(k: Any, n_classes: int) -> int:
+    return max(1, min(int(k), int(n_classes)))
+
+
+def _topk_dicts(idx_row: np.ndarray, score_row: np.ndarray) -> List[Dict[str, Any]]:
+    # plain Python numbers: the result goes through requests.post(json=...) (app.py:146)
+    return [{"index": int(i), "score": float(s)} for i, s in zip(idx_row, score_row)]
+
+
+def _error_envelope(payload: Dict[str, Any]) -> Dict[str, Any]:
+    return {
+        "op": OP_NAME,
+        "fallback": "cpu",
+        "reason": payload.get("fallback_reason", "CUDA unavailable"),
+        "topk": [],
+    }
+
+
+@register_op(OP_NAME)
+def run(payload: Dict[str, Any], ctx: Dict[str, Any] = None) -> Dict[str, Any]:
+    """
+    B200-backed text classification.
+
+    Uses:
+      - payload["model_path"] OR env CUDA_MODEL_PATH / TPU_MODEL_PATH OR /models/model_b200.b2m
+      - payload["topk"] default 5
+      - payload["items"] (list of texts)  OR  payload["input"] (flat list[int], one row of token ids)
+      - payload["max_len"] default 128, payload["batch"] default 1024, payload["vocab_path"] optional
+      - payload["allow_fallback"] default True
+    """
+    ctx = ctx or {}
+    payload = payload or {}
+
+    t0 = time.time()
+    allow_fallback = payload.get("allow_fallback", True)
+
+    try:
+        model_path = get_model_path(payload.get("model_path"))
+        max_len = int(payload.get("max_len", 128))
+        batch = int(payload.get("batch", 1024))
+        if max_len <= 0 or batch <= 0:
+            raise ValueError("payload.max_len and payload.batch must be positive integers")
+        h = get_cuda_handle(model_path, payload.get("vocab_path"), max_len=max_len, max_batch=batch)
+        eng = h.interpreter
+        n_classes = int(h.output_details[0]["shape"][-1])
+        k = _clamp_k(payload.get("topk", 5), n_classes)
+
+        items = payload.get("items")
+        if items is not None:
+            if not isinstance(items, list):
+                raise ValueError("payload.items must be a list of strings")
+            texts = ["" if x is None else str(x) for x in items]
+            lo, hi, rank, world = _shard.my_slice(len(texts))
+            out = eng.classify(texts[lo:hi], max_len=max_len, topk=k,
+                               want_logits=bool(payload.get("return_logits")))
+            hist, metrics = _shard.reduce_job(out["histogram"], out["metrics"], eng.device)
+            first = _topk_dicts(out["top_idx"][0], out["top_score"][0]) if hi > lo else []
+            result = {
+                "op": OP_NAME,
+                "model_path": h.model_path,
+                "topk": first,
+                "elapsed_ms": 0.0,
+                "items_count": len(texts),
+                "labels": out["labels"].tolist(),
+                "label_histogram": [int(v) for v in hist],
+                "metrics": metrics,
+            }
+            if world > 1:
+                result["shard"] = {"rank": rank, "world_size": world, "start": lo, "end": hi}
+            if payload.get("return_results"):
+                result["results"] = [{"topk": _topk_dicts(i, s)}
+                                     for i, s in zip(out["top_idx"], out["top_score"])]
+            if payload.get("return_logits"):
+                result["logits"] = out["logits"].tolist()
+            result["elapsed_ms"] = (time.time() - t0) * 1000.0
+            return result
+
+        if "input" not in payload:
+            raise ValueError('payload missing required key: "input"')
+
+        input_details = h.input_details[0]
+        shape = (1, max_len)
+        dtype = input_details["dtype"]
+
+        arr = np.array(payload["input"], dtype=dtype)
+
+        expected = int(np.prod(shape))
+        if arr.size != expected:
+            raise ValueError(
+                f"Input size mismatch. Got {arr.size}, expected {expected} for shape {shape}."
+            )
+
+        arr = arr.reshape(shape)
+        out = eng.classify_ids(arr, (arr != PAD_ID).astype(np.uint8), topk=k)
+
+        return {
+            "op": OP_NAME,
+            "model_path": h.model_path,
+            "topk": _topk_dicts(out["top_idx"][0], out["top_score"][0]),
+            "elapsed_ms": (time.time() - t0) * 1000.0,
+        }
+
+    except Exception as e:
+        if allow_fallback:
+            return {
+                **_error_envelope({"fallback_reason": str(e), **payload}),
+                "elapsed_ms": (time.time() - t0) * 1000.0,
+            }
+        raise

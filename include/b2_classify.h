@@ -1,0 +1,139 @@
+/* b2_classify.h — C ABI of libb2classify.so, the B200 back end of agent-tpu's `map_classify_tpu`
+ * and `map_tokenize` ops.
+ *
+ * The reference has no FFI: its back end is a Python object (a TFLite interpreter) reached from
+ * two call sites. Each entry point below names the reference call it stands in for; paths are
+ * relative to the reference repository root. INTEGRATION.md shows the ctypes binding.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a B2_ERR_* code; b2_last_error() then returns a
+ *     human-readable message for the calling thread;
+ *   - the caller owns every buffer it passes; the library owns device memory, streams and events;
+ *   - calls are blocking: results are complete when the call returns;
+ *   - a handle is bound to one CUDA device and must be used by one thread at a time (the agent runs
+ *     tasks inline, one at a time: app.py:286);
+ *   - there is no CPU fallback: without a usable CUDA device b2_create fails.
+ */
+#ifndef B2_CLASSIFY_H
+#define B2_CLASSIFY_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_OK 0
+#define B2_ERR_ARG 1     /* bad argument */
+#define B2_ERR_CUDA 2    /* CUDA runtime / driver error */
+#define B2_ERR_IO 3      /* file missing or unreadable */
+#define B2_ERR_FORMAT 4  /* file present but not in the expected format */
+#define B2_ERR_LIMIT 5   /* request exceeds a limit of the handle */
+
+typedef struct b2_handle b2_handle;
+
+/* Replaces the arguments of get_tpu_handle(model_path) (ops/_tpu_runtime.py:34). */
+typedef struct b2_config {
+  int32_t struct_size;      /* sizeof(b2_config) */
+  int32_t device;           /* CUDA device ordinal */
+  const char* model_path;   /* .b2m model file; NULL gives a tokenizer-only handle */
+  const char* vocab_path;   /* vocab.txt, one WordPiece per line; NULL gives a handle without tokenizer */
+  const char* unicode_path; /* bert_unicode.bin (required with vocab_path) */
+  int32_t max_batch;        /* items per encoder pass, 0 = 1024 */
+  int32_t max_len;          /* largest padded length this handle will be asked for, 0 = 128 */
+} b2_config;
+
+/* Replaces interpreter.get_input_details() / get_output_details() (ops/_tpu_runtime.py:59-60). */
+typedef struct b2_model_info {
+  int32_t hidden, layers, heads, intermediate;
+  int32_t vocab_size, max_positions, num_labels, tokenizer_vocab_size;
+  int32_t max_batch, max_len, device, sm_count;
+  int64_t weight_bytes, activation_bytes;
+} b2_model_info;
+
+/* Per-call counters and device timings (CUDA events on the library's stream). The reference
+ * reports only wall-clock elapsed_ms (ops/map_classify_tpu.py:45,81). */
+typedef struct b2_metrics {
+  int32_t struct_size; /* sizeof(b2_metrics), set by the caller */
+  int32_t profiled;    /* 1 if per-kernel timings below were collected (b2_set_profiling) */
+  int64_t items, tokens, padded_tokens, batches;
+  int64_t kernel_launches;
+  int64_t h2d_bytes, d2h_bytes;
+  double gpu_ms_total; /* first kernel to last kernel, all batches */
+  /* per kernel kind, summed over launches (only when profiled): */
+  double ms_tokenize, ms_embed, ms_gemm_qkv, ms_attention, ms_gemm_attn_out, ms_layernorm,
+      ms_gemm_ffn1, ms_gemm_ffn2, ms_pooler, ms_head;
+  int64_t n_tokenize, n_embed, n_gemm_qkv, n_attention, n_gemm_attn_out, n_layernorm, n_gemm_ffn1,
+      n_gemm_ffn2, n_pooler, n_head;
+} b2_metrics;
+
+/* Replaces nvidia-smi parsing in _parse_nvidia_smi (worker_sizing.py:139-161). */
+typedef struct b2_device_info {
+  char name[128];
+  int64_t total_memory_bytes;
+  int32_t sm_count, cc_major, cc_minor, l2_bytes;
+} b2_device_info;
+
+/* Thread-local message for the last failing call. No reference counterpart (the reference raises
+ * Python exceptions: ops/_tpu_runtime.py:49-53). */
+const char* b2_last_error(void);
+
+/* Number of CUDA devices, 0 if none (no error). Replaces list_edge_tpus() (ops/_tpu_runtime.py:48). */
+int32_t b2_device_count(void);
+int b2_get_device_info(int32_t device, b2_device_info* out);
+
+/* Load model + tokenizer onto a device: make_interpreter + allocate_tensors
+ * (ops/_tpu_runtime.py:55-56). */
+int b2_create(const b2_config* config, b2_handle** out);
+void b2_destroy(b2_handle* h);
+int b2_get_model_info(b2_handle* h, b2_model_info* out);
+/* 1: time every kernel launch with CUDA events (adds one stream sync per batch); 0: off. */
+int b2_set_profiling(b2_handle* h, int32_t on);
+
+/* WordPiece tokenize-and-pad. utf8 holds the n items back to back, item i is bytes
+ * [offsets[i], offsets[i+1]). ids: [n, max_len] int32, mask: [n, max_len] uint8 (either may be
+ * NULL). No reference counterpart; shared by map_tokenize (mode "wordpiece") and
+ * map_classify_tpu. Host pointers. */
+int b2_tokenize(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n, int32_t max_len,
+                int32_t* ids, uint8_t* mask, b2_metrics* metrics);
+/* Same with every pointer in device memory on the handle's device (inputs already resident). */
+int b2_tokenize_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offsets, int64_t n,
+                       int64_t n_bytes, int32_t max_len, int32_t* d_ids, uint8_t* d_mask,
+                       b2_metrics* metrics);
+
+/* Classify n text items: tokenize, encoder forward, head. Replaces set_tensor / invoke /
+ * get_tensor / _topk for a whole job (ops/map_classify_tpu.py:61-75, 15-19).
+ *   top_idx, top_score: [n, topk]  descending by score (softmax probability); k clamped like the
+ *                       reference must be done by the caller: 1 <= topk <= num_labels
+ *   labels:    [n] arg-max class                          (may be NULL)
+ *   histogram: [num_labels] counts of labels, overwritten (may be NULL)
+ *   logits:    [n, num_labels] float32                    (may be NULL)
+ * Host pointers. */
+int b2_classify_text(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                     int32_t max_len, int32_t topk, int32_t* top_idx, float* top_score,
+                     int32_t* labels, int64_t* histogram, float* logits, b2_metrics* metrics);
+/* Same with text, offsets and all outputs in device memory. */
+int b2_classify_text_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offsets, int64_t n,
+                            int64_t n_bytes, int32_t max_len, int32_t topk, int32_t* d_top_idx,
+                            float* d_top_score, int32_t* d_labels, int64_t* d_histogram,
+                            float* d_logits, b2_metrics* metrics);
+/* Classify n pre-tokenised rows: ids [n, max_len] int32, mask [n, max_len] uint8 (1 = token).
+ * This is the v0 contract's `input: list[int]` (ops/map_classify_tpu.CONTRACT.md:7-8,
+ * ops/map_classify_tpu.py:61-72) widened to n rows. Host pointers. */
+int b2_classify_ids(b2_handle* h, const int32_t* ids, const uint8_t* mask, int64_t n, int32_t max_len,
+                    int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels,
+                    int64_t* histogram, float* logits, b2_metrics* metrics);
+
+/* Fixed-width chunking in code points: _chunk_text (ops/map_tokenize.py:6-9) over items.
+ * Pass 1: code points per item -> counts[n]. Pass 2: chunk j of item i starts at byte
+ * bounds[chunk_base[i] + j] of utf8, where chunk_base is the exclusive prefix sum of
+ * ceil(counts[i] / chunk_size) computed by the caller. Host pointers. */
+int b2_chunk_count(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                   int64_t* counts);
+int b2_chunk_bounds(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                    int64_t chunk_size, const int64_t* chunk_base, int64_t n_chunks, int64_t* bounds);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2_CLASSIFY_H */
