@@ -664,6 +664,10 @@ int b2_set_profiling(b2_handle* h, int32_t on) {
   return B2_OK;
 }
 
+uint64_t b2_get_stream(b2_handle* h) {
+  return h ? static_cast<uint64_t>(reinterpret_cast<uintptr_t>(h->stream)) : 0;
+}
+
 int b2_tokenize_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offsets, int64_t n,
                        int64_t n_bytes, int32_t max_len, int32_t* d_ids, uint8_t* d_mask,
                        b2_metrics* metrics) {

@@ -103,6 +103,8 @@ def load_library():
     lib.b2_destroy.restype = None
     lib.b2_get_model_info.argtypes = [P, C.POINTER(ModelInfo)]
     lib.b2_set_profiling.argtypes = [P, I32]
+    lib.b2_get_stream.argtypes = [P]
+    lib.b2_get_stream.restype = C.c_uint64
     lib.b2_tokenize.argtypes = [P, P, P, I64, I32, P, P, C.POINTER(Metrics)]
     lib.b2_tokenize_device.argtypes = [P, P, P, I64, I64, I32, P, P, C.POINTER(Metrics)]
     lib.b2_classify_text.argtypes = [P, P, P, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
@@ -176,6 +178,11 @@ class Engine:
     def handle(self) -> C.c_void_p:
         return self._h
 
+    @property
+    def stream(self) -> int:
+        """cudaStream_t (as int) that this engine's kernels run on."""
+        return int(self._lib.b2_get_stream(self._h))
+
     def set_profiling(self, on: bool) -> None:
         _check(self._lib, self._lib.b2_set_profiling(self._h, 1 if on else 0))
 
@@ -202,9 +209,11 @@ class Engine:
                 np.empty((n, Cn), dtype=np.float32) if want_logits else None)
 
     def classify_packed(self, blob: np.ndarray, offsets: np.ndarray, max_len: int = 128, topk: int = 5,
-                        want_logits: bool = False) -> dict:
+                        want_logits: bool = False, outputs=None) -> dict:
+        """`outputs` may supply (top_idx, top_score, labels, hist, logits) arrays to fill, e.g. views
+        of pinned host memory; otherwise fresh numpy arrays are returned."""
         n = len(offsets) - 1
-        top_idx, top_score, labels, hist, logits = self._outputs(n, topk, want_logits)
+        top_idx, top_score, labels, hist, logits = outputs or self._outputs(n, topk, want_logits)
         m = Metrics(struct_size=C.sizeof(Metrics))
         _check(self._lib, self._lib.b2_classify_text(self._h, _ptr(blob), _ptr(offsets), n, int(max_len),
                                                      int(topk), _ptr(top_idx), _ptr(top_score), _ptr(labels),

@@ -89,6 +89,9 @@ void b2_destroy(b2_handle* h);
 int b2_get_model_info(b2_handle* h, b2_model_info* out);
 /* 1: time every kernel launch with CUDA events (adds one stream sync per batch); 0: off. */
 int b2_set_profiling(b2_handle* h, int32_t on);
+/* The cudaStream_t every kernel of this handle is launched on, as an integer, so a caller can
+ * record its own CUDA events on it. No reference counterpart. */
+uint64_t b2_get_stream(b2_handle* h);
 
 /* WordPiece tokenize-and-pad. utf8 holds the n items back to back, item i is bytes
  * [offsets[i], offsets[i+1]). ids: [n, max_len] int32, mask: [n, max_len] uint8 (either may be

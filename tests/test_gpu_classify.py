@@ -1,0 +1,204 @@
+"""map_classify parity on the GPU, through the C ABI and through the op.
+
+Tolerances are the ones BASELINE.json states: token ids / masks bit-exact (test_gpu_tokenizer.py);
+logits within 2e-2 max-abs of the fp32 oracle; predicted labels identical wherever the oracle's
+top-2 margin exceeds 0.05. The oracle is oracle/bert_oracle.py (pinned to transformers'
+BertForSequenceClassification; NOT the reference, which has no model — SURVEY.md §0)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+LOGIT_TOL = 2e-2
+MARGIN = 0.05
+
+
+def _load_golden(golden_dir, name):
+    with open(os.path.join(golden_dir, f"classify_{name}_texts.json"), encoding="utf-8") as f:
+        meta = json.load(f)
+    z = np.load(os.path.join(golden_dir, f"classify_{name}_golden.npz"))
+    return meta, z
+
+
+def _check_against(logits_ref, out, k):
+    logits = out["logits"]
+    assert np.abs(logits - logits_ref).max() <= LOGIT_TOL
+    srt = np.sort(logits_ref, axis=1)
+    sure = (srt[:, -1] - srt[:, -2]) > MARGIN
+    assert (out["labels"][sure] == logits_ref.argmax(1)[sure]).all()
+    # head consistency: labels / top-k / scores / histogram all derive from the device logits
+    assert (out["labels"] == logits.argmax(1)).all()
+    assert (out["top_idx"][:, 0] == out["labels"]).all()
+    e = np.exp(logits - logits.max(1, keepdims=True))
+    probs = e / e.sum(1, keepdims=True)
+    assert np.abs(np.take_along_axis(probs, out["top_idx"], 1) - out["top_score"]).max() < 1e-5
+    assert (np.diff(out["top_score"], axis=1) <= 1e-7).all()
+    assert (out["histogram"] == np.bincount(out["labels"], minlength=logits.shape[1])).all()
+    assert out["top_idx"].shape[1] == k
+
+
+@pytest.fixture(scope="module")
+def tiny_engine(tiny_model, vocab_path):
+    from ops import _cuda_runtime as rt
+    eng = rt.Engine(tiny_model, vocab_path, max_batch=64, max_len=512)
+    yield eng
+    eng.close()
+
+
+@pytest.fixture(scope="module")
+def base_engine(base_model, vocab_path):
+    from ops import _cuda_runtime as rt
+    eng = rt.Engine(base_model, vocab_path, max_batch=1024, max_len=128)
+    yield eng
+    eng.close()
+
+
+def test_tiny_model_against_committed_golden(tiny_engine, golden_dir):
+    meta, z = _load_golden(golden_dir, "tiny")
+    out = tiny_engine.classify(meta["texts"], 128, 3, want_logits=True)   # 256 items = 4 batches of 64
+    _check_against(z["logits"], out, 3)
+    assert out["metrics"]["tokens"] == int(z["lens"].sum()) and out["metrics"]["batches"] == 4
+
+
+def test_tiny_model_long_documents_s512(tiny_engine, golden_dir):
+    meta, z = _load_golden(golden_dir, "tiny512")
+    out = tiny_engine.classify(meta["texts"], 512, 5, want_logits=True)
+    _check_against(z["logits"], out, 5)
+
+
+def test_base_model_against_committed_golden(base_engine, golden_dir):
+    meta, z = _load_golden(golden_dir, "base")
+    out = base_engine.classify(meta["texts"], 128, 5, want_logits=True)
+    _check_against(z["logits"], out, 5)
+    assert len(set(out["labels"].tolist())) >= 2      # the fixture exercises more than one class
+
+
+def test_base_model_against_live_oracle(base_engine, base_model, vocab_path, sentences):
+    import bert_oracle as bo
+    texts = sentences[1000:1048]
+    cfg, W = bo.load_model(base_model)
+    ids, mask = bo.tokenize(vocab_path, texts, 128)
+    ref = bo.forward(cfg, W, ids, mask)
+    out = base_engine.classify(texts, 128, 5, want_logits=True)
+    _check_against(ref, out, 5)
+
+
+def test_explicit_tensor_model_file_equals_synthetic(tiny_model, vocab_path, work_dir, sentences):
+    """kind 0 (f32 tensors in the file) loads to the same network as kind 1 (seed): this also
+    proves the device-side synthetic initialiser is bit-identical to the host twin."""
+    import model_file as mf
+    from ops import _cuda_runtime as rt
+    cfg = mf.read_header(tiny_model)
+    p = mf.write_model_file(os.path.join(work_dir, "tiny_explicit.b2m"), cfg, tensors=mf.load_tensors(tiny_model))
+    a = rt.Engine(tiny_model, vocab_path, max_batch=32, max_len=128)
+    b = rt.Engine(p, vocab_path, max_batch=32, max_len=128)
+    try:
+        oa = a.classify(sentences[:40], 128, 2, want_logits=True)
+        ob = b.classify(sentences[:40], 128, 2, want_logits=True)
+        assert (oa["logits"] == ob["logits"]).all() and (oa["top_idx"] == ob["top_idx"]).all()
+    finally:
+        a.close(); b.close()
+
+
+def test_batch_size_and_order_independence(tiny_model, vocab_path, sentences):
+    from ops import _cuda_runtime as rt
+    texts = sentences[:150] + [""] + sentences[150:200]
+    a = rt.Engine(tiny_model, vocab_path, max_batch=64, max_len=128)
+    b = rt.Engine(tiny_model, vocab_path, max_batch=7, max_len=128)
+    try:
+        oa = a.classify(texts, 128, 2, want_logits=True)
+        ob = b.classify(texts, 128, 2, want_logits=True)
+        assert (oa["logits"] == ob["logits"]).all() and (oa["histogram"] == ob["histogram"]).all()
+        perm = np.random.default_rng(0).permutation(len(texts))
+        oc = a.classify([texts[i] for i in perm], 128, 2, want_logits=True)
+        assert (oc["logits"] == oa["logits"][perm]).all()
+        assert (oc["histogram"] == oa["histogram"]).all()
+    finally:
+        a.close(); b.close()
+
+
+def test_ids_entry_point_equals_text_entry_point(tiny_engine, sentences):
+    texts = sentences[:70]
+    ids, mask, _ = tiny_engine.tokenize(texts, 128)
+    a = tiny_engine.classify(texts, 128, 3, want_logits=True)
+    b = tiny_engine.classify_ids(ids, mask, 3, want_logits=True)
+    assert (a["logits"] == b["logits"]).all() and (a["top_idx"] == b["top_idx"]).all()
+
+
+def test_limits_and_errors(tiny_engine):
+    from ops import _cuda_runtime as rt
+    with pytest.raises(rt.B2Error):
+        tiny_engine.classify(["x"], 128, 99)            # topk > num_labels
+    with pytest.raises(rt.B2Error):
+        tiny_engine.classify(["x"], 1024, 1)            # beyond the handle's max_len
+    with pytest.raises(rt.B2Error):
+        tiny_engine.classify(["x"], 100, 1)             # not a multiple of 128
+    out = tiny_engine.classify([], 128, 2)
+    assert out["top_idx"].shape == (0, 2) and out["histogram"].sum() == 0
+
+
+def test_full_batch_job_properties(base_engine, sentences):
+    """Eight full 1,024-item batches (BASELINE config 3's batch shape): histogram sums to n, rows of a
+    repeated input repeat, profiling accounts for every launch."""
+    texts = (sentences * 4)[:8192]
+    base_engine.set_profiling(True)
+    try:
+        out = base_engine.classify(texts, 128, 5)
+    finally:
+        base_engine.set_profiling(False)
+    n = len(sentences)
+    assert out["histogram"].sum() == len(texts)
+    assert (out["labels"][:n] == out["labels"][n:2 * n]).all()
+    assert (out["top_score"][:n] == out["top_score"][2 * n:3 * n]).all()
+    m = out["metrics"]
+    assert m["batches"] == 8 and m["items"] == 8192
+    assert sum(v["launches"] for v in m["kernels"].values()) == 8 * (1 + 1 + 12 * 7 + 2)
+    assert 0 < sum(v["ms"] for v in m["kernels"].values()) <= m["gpu_ms_total"] * 1.05
+
+
+def test_op_envelope_on_gpu(base_model, vocab_path, clean_env, sentences, golden_dir):
+    from ops import _cuda_runtime as rt
+    from ops import map_classify_tpu as op
+    rt.reset_cache()
+    clean_env.setenv("CUDA_MODEL_PATH", base_model)
+    texts = sentences[:33]
+    r = op.run({"items": texts, "topk": 3, "return_results": True})
+    assert list(r.keys())[:4] == ["op", "model_path", "topk", "elapsed_ms"]      # v0 keys first, same order
+    assert r["op"] == "map_classify_tpu" and r["model_path"] == base_model
+    assert len(r["topk"]) == 3 and all(set(t) == {"index", "score"} for t in r["topk"])
+    assert all(type(t["index"]) is int and type(t["score"]) is float for t in r["topk"])
+    assert r["items_count"] == 33 and len(r["labels"]) == 33 and sum(r["label_histogram"]) == 33
+    assert r["results"][0]["topk"] == r["topk"]
+    json.dumps(r)                                                               # pure JSON (app.py:146)
+    # topk is clamped like the reference's _topk
+    assert len(op.run({"items": texts[:2], "topk": 0})["topk"]) == 1
+    assert len(op.run({"items": texts[:2], "topk": 999})["topk"]) == 16
+    # the handle is cached by model path (ops/_tpu_runtime.py:42-43)
+    h1 = rt.get_cuda_handle(base_model); h2 = rt.get_cuda_handle(base_model)
+    assert h1.interpreter is h2.interpreter
+    # v0 `input`: one pre-tokenised row
+    ids, mask, _ = h1.interpreter.tokenize(texts[:1], 128)
+    v0 = op.run({"input": ids[0].tolist(), "topk": 3})
+    assert list(v0.keys()) == ["op", "model_path", "topk", "elapsed_ms"]
+    assert [t["index"] for t in v0["topk"]] == [t["index"] for t in r["topk"]]
+    # error routes (ops/map_classify_tpu.py:63-67, 84-90)
+    bad = op.run({"input": [1, 2, 3]})
+    assert bad["fallback"] == "cpu" and bad["topk"] == [] and bad["reason"] == \
+        "Input size mismatch. Got 3, expected 128 for shape (1, 128)."
+    assert op.run({})["reason"] == 'payload missing required key: "input"'
+    with pytest.raises(ValueError):
+        op.run({"input": [1, 2, 3], "allow_fallback": False})
+    missing = op.run({"items": ["x"], "model_path": "/nonexistent/model.b2m"})
+    assert missing["reason"] == "CUDA model not found: /nonexistent/model.b2m"
+    rt.reset_cache()
+
+
+def test_worker_profile_reports_this_gpu(clean_env):
+    import worker_sizing as ws
+    gpu = ws.build_worker_profile()["gpu"]
+    assert gpu["gpu_present"] and gpu["gpu_count"] >= 1 and gpu["max_gpu_workers"] == gpu["gpu_count"]
+    d = gpu["devices"][0]
+    assert "B200" in d["name"] and d["sm_count"] == 148 and d["total_memory_bytes"] > 150 * 2 ** 30

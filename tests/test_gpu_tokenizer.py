@@ -1,0 +1,114 @@
+"""GPU tokenizer and chunker parity through the C ABI (b2_tokenize, b2_chunk_*).
+
+Bar: bit-exact. Oracles: the committed golden ids (tokenizers 0.22.2 BertWordPieceTokenizer), the
+same library called live on seeded inputs, and for chunking the reference's own recorded outputs
+(ops/map_tokenize.py via tests/golden/reference_golden.json)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def tok_engine(vocab_path):
+    from ops import _cuda_runtime as rt
+    eng = rt.Engine(None, vocab_path, max_batch=1, max_len=512)
+    yield eng
+    eng.close()
+
+
+def _golden(golden_dir):
+    with open(os.path.join(golden_dir, "tokenizer_golden.json"), encoding="utf-8") as f:
+        return json.load(f)
+
+
+def test_matches_committed_golden(tok_engine, golden_dir, vocab_sha):
+    g = _golden(golden_dir)
+    assert g["vocab_sha256"] == vocab_sha
+    for case in g["cases"]:
+        ml = case["max_len"]
+        ids, mask, _ = tok_engine.tokenize(g["texts"], ml)
+        for i, want in enumerate(case["ids"]):
+            n = len(want)
+            assert ids[i, :n].tolist() == want, (ml, g["texts"][i][:50])
+            assert not ids[i, n:].any() and mask[i, :n].all() and not mask[i, n:].any()
+
+
+def test_matches_live_oracle_on_seeded_sentences(tok_engine, vocab_path, sentences):
+    import bert_oracle as bo
+    for ml in (128, 64, 7):
+        ids, mask, _ = tok_engine.tokenize(sentences, ml)
+        rids, rmask = bo.tokenize(vocab_path, sentences, ml)
+        assert (ids == rids).all() and (mask == rmask).all()
+
+
+def test_unicode_sweep_against_live_oracle(tok_engine, vocab_path):
+    """Every BMP code point and a sample of the astral planes, 48 per line between ASCII words."""
+    import bert_oracle as bo
+    cps = [c for c in range(1, 0x10000) if not 0xD800 <= c <= 0xDFFF] + list(range(0x10000, 0x110000, 37))
+    lines = []
+    for i in range(0, len(cps), 48):
+        lines.append("ab " + " x".join(chr(c) for c in cps[i:i + 48]) + " yz")
+    ids, mask, _ = tok_engine.tokenize(lines, 256)
+    rids, rmask = bo.tokenize(vocab_path, lines, 256)
+    bad = np.nonzero((ids != rids).any(1))[0]
+    assert bad.size == 0, [hex(cps[b * 48]) for b in bad[:10]]
+    assert (mask == rmask).all()
+
+
+def test_ragged_and_empty_inputs(tok_engine, vocab_path):
+    import bert_oracle as bo
+    ids, mask, _ = tok_engine.tokenize([], 128)
+    assert ids.shape == (0, 128)
+    texts = ["", "a", " ", "word " * 5000, "z" * 100000, "é" * 333, "\n"] * 3
+    ids, mask, _ = tok_engine.tokenize(texts, 128)
+    rids, rmask = bo.tokenize(vocab_path, texts, 128)
+    assert (ids == rids).all() and (mask == rmask).all()
+    assert (ids[0, :2] == [101, 102]).all() and mask[0].sum() == 2
+
+
+def test_million_lines_properties(tok_engine, sentences):
+    """Config 2 size (1M lines): row-wise determinism, structure of every row, agreement with the
+    small run the oracle has already checked."""
+    base_ids, base_mask, _ = tok_engine.tokenize(sentences, 128)
+    reps = 1_000_000 // len(sentences) + 1
+    big = (sentences * reps)[:1_000_000]
+    ids, mask, m = tok_engine.tokenize(big, 128)
+    assert ids.shape == (1_000_000, 128)
+    n = len(sentences)
+    full = (1_000_000 // n) * n
+    assert (ids[:full].reshape(-1, n, 128) == base_ids[None]).all()
+    assert (mask[:full].reshape(-1, n, 128) == base_mask[None]).all()
+    lens = mask.sum(1)
+    assert (ids[:, 0] == 101).all() and (ids[np.arange(len(ids)), lens - 1] == 102).all()
+    assert ((ids != 0) == (mask != 0)).all()
+    assert m["items"] == 1_000_000
+
+
+def test_map_tokenize_matches_reference_outputs(ref_golden, clean_env):
+    from ops import map_tokenize as tok
+    for case in ref_golden["map_tokenize"]:
+        assert tok.map_tokenize_op(case["payload"]) == case["result"], case["payload"]
+
+
+def test_map_tokenize_chunking_large(clean_env, sentences):
+    from ops import map_tokenize as tok
+    items = sentences[:500] + ["naïve café 中文字 😀" * 50, "", None, 12345]
+    for cs in (1, 7, 1024):
+        r = tok.map_tokenize_op({"items": items, "chunk_size": cs})
+        strs = ["" if x is None else str(x) for x in items]
+        want = [s[i:i + cs] for s in strs for i in range(0, len(s), cs)]
+        assert r["tokens"] == want and r["count"] == len(want)
+        assert r["total_chars"] == sum(len(s) for s in strs) and r["items_count"] == len(items)
+
+
+def test_map_tokenize_wordpiece_mode(vocab_path, clean_env, sentences):
+    import bert_oracle as bo
+    from ops import map_tokenize as tok
+    r = tok.map_tokenize_op({"items": sentences[:10], "mode": "wordpiece", "max_len": 64, "vocab_path": vocab_path})
+    rids, rmask = bo.tokenize(vocab_path, sentences[:10], 64)
+    assert r["ok"] and r["input_ids"] == rids.tolist() and r["attention_mask"] == rmask.tolist()
+    assert r["count"] == int(rmask.sum())

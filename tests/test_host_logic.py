@@ -1,0 +1,66 @@
+"""Host-side pieces that need no GPU: synthetic data, model file, packing, sharding."""
+import os
+
+import numpy as np
+import pytest
+
+import model_file as mf
+import synth
+from ops import _cuda_runtime as rt
+from ops import _shard
+
+
+def test_vocab_layout():
+    v = synth.build_vocab()
+    assert len(v) == 30522 and len(set(v)) == 30522
+    assert (v[0], v[100], v[101], v[102], v[103]) == ("[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]")
+
+
+def test_sentences_are_deterministic_and_fit():
+    g = synth.SentenceGenerator()
+    a, b = g.sentences(50), g.sentences(50)
+    assert a == b and all(s.endswith(".") for s in a)
+
+
+def test_pack_items_layout():
+    blob, off = rt.pack_items(["ab", "", "é", "\ud800"])
+    assert off.tolist() == [0, 2, 2, 4, 7] and blob.dtype == np.uint8 and blob.size == 7
+    blob, off = rt.pack_items([])
+    assert off.tolist() == [0] and blob.size == 0
+    assert synth.pack_items(["ab", "é"])[1].tolist() == [0, 2, 4]
+
+
+def test_model_file_roundtrip_and_synthetic_stats(tmp_path):
+    p = mf.write_model_file(str(tmp_path / "m.b2m"), mf.BERT_TINY)
+    cfg = mf.read_header(p)
+    assert (cfg.hidden, cfg.layers, cfg.heads, cfg.num_labels, cfg.kind) == (128, 2, 2, 5, 1)
+    assert os.path.getsize(p) == mf.HEADER_SIZE
+    t = mf.load_tensors(p)
+    names = [n for n, *_ in mf.tensor_specs(cfg)]
+    assert list(t.keys()) == names
+    w = t["word_emb"]
+    assert abs(float(w.std()) - cfg.init_std) < 2e-3 and abs(float(w.mean())) < 1e-3
+    assert abs(float(t["emb_ln_g"].mean()) - 1.0) < 0.02
+    # same seed -> same bits; another tensor id -> another stream
+    a = mf.synthetic_tensor(1234, 0, 1000, np.float32(1e-6), np.float32(0))
+    assert (a == mf.synthetic_tensor(1234, 0, 1000, np.float32(1e-6), np.float32(0))).all()
+    assert (a != mf.synthetic_tensor(1234, 1, 1000, np.float32(1e-6), np.float32(0))).any()
+    # explicit-tensor files carry the same values
+    p2 = mf.write_model_file(str(tmp_path / "m2.b2m"), cfg, tensors=t)
+    t2 = mf.load_tensors(p2)
+    assert mf.read_header(p2).kind == 0 and all((t[k] == t2[k]).all() for k in t)
+
+
+def test_slice_bounds_cover_without_overlap():
+    for n in (0, 1, 7, 8, 1000003):
+        for w in (1, 2, 4, 8):
+            cuts = [_shard.slice_bounds(n, r, w) for r in range(w)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == n
+            assert all(cuts[i][1] == cuts[i + 1][0] for i in range(w - 1))
+            assert max(hi - lo for lo, hi in cuts) - min(hi - lo for lo, hi in cuts) <= 1
+
+
+def test_shard_is_inert_without_process_group():
+    assert _shard.my_slice(10) == (0, 10, 0, 1)
+    h, m = _shard.reduce_job(np.arange(4), {"items": 3})
+    assert h.tolist() == [0, 1, 2, 3] and m == {"items": 3}

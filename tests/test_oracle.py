@@ -1,0 +1,80 @@
+"""The oracle against its pins: the reference's golden top-k, the committed tokenizer / logits
+vectors, and transformers' BertForSequenceClassification. CPU only."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import bert_oracle as bo
+import model_file as mf
+
+
+def test_topk_restatement_matches_reference_golden(ref_golden):
+    for case in ref_golden["topk"]:
+        scores = np.array(case["scores"], dtype=np.float32)
+        got = bo.topk(scores, case["k"])
+        want = case["out"]
+        assert len(got) == len(want)
+        # order among exactly equal scores is unspecified in the reference (unstable sort)
+        assert [g["score"] for g in got] == [w["score"] for w in want]
+        if len(set(case["scores"])) == len(case["scores"]):
+            assert [g["index"] for g in got] == [w["index"] for w in want]
+
+
+def test_vocab_is_the_one_the_golden_vectors_were_made_with(golden_dir, vocab_sha):
+    with open(os.path.join(golden_dir, "tokenizer_golden.json"), encoding="utf-8") as f:
+        g = json.load(f)
+    assert g["vocab_sha256"] == vocab_sha
+
+
+def test_tokenizer_oracle_matches_committed_golden(golden_dir, vocab_path):
+    with open(os.path.join(golden_dir, "tokenizer_golden.json"), encoding="utf-8") as f:
+        g = json.load(f)
+    for case in g["cases"]:
+        ids, mask = bo.tokenize(vocab_path, g["texts"], case["max_len"])
+        for row, m, want in zip(ids, mask, case["ids"]):
+            n = int(m.sum())
+            assert row[:n].tolist() == want
+            assert not row[n:].any() and m[:n].all() and not m[n:].any()
+
+
+def test_forward_matches_transformers_bert(tiny_model, vocab_path, sentences):
+    cfg, W = bo.load_model(tiny_model)
+    ids, mask = bo.tokenize(vocab_path, sentences[:24] + ["", "x"], 128)
+    mine = bo.forward(cfg, W, ids, mask)
+    model = bo.hf_model(cfg, W)
+    with torch.no_grad():
+        ref = model(input_ids=torch.from_numpy(ids).long(), attention_mask=torch.from_numpy(mask).long()).logits.numpy()
+    assert np.abs(mine - ref).max() < 2e-5
+
+
+def test_forward_matches_committed_golden_tiny(golden_dir, tiny_model, vocab_path):
+    with open(os.path.join(golden_dir, "classify_tiny_texts.json"), encoding="utf-8") as f:
+        meta = json.load(f)
+    z = np.load(os.path.join(golden_dir, "classify_tiny_golden.npz"))
+    cfg, W = bo.load_model(tiny_model)
+    assert mf.config_dict(cfg) == meta["model"]
+    ids, mask = bo.tokenize(vocab_path, meta["texts"], meta["max_len"])
+    assert (mask.sum(1) == z["lens"]).all() and int(ids.astype(np.int64).sum()) == int(z["ids_crc"][0])
+    assert np.abs(bo.forward(cfg, W, ids, mask) - z["logits"]).max() < 1e-4
+
+
+def test_forward_matches_committed_golden_base_sample(golden_dir, base_model, vocab_path):
+    with open(os.path.join(golden_dir, "classify_base_texts.json"), encoding="utf-8") as f:
+        meta = json.load(f)
+    z = np.load(os.path.join(golden_dir, "classify_base_golden.npz"))
+    cfg, W = bo.load_model(base_model)
+    pick = [0, 3, 9, 100, 255]
+    ids, mask = bo.tokenize(vocab_path, [meta["texts"][i] for i in pick], meta["max_len"])
+    assert np.abs(bo.forward(cfg, W, ids, mask) - z["logits"][pick]).max() < 1e-4
+
+
+def test_bf16_emulation_predicts_the_stated_tolerance(base_model, vocab_path, sentences):
+    """The 2e-2 logit tolerance (BASELINE.json) has to be reachable with bf16 activations at all."""
+    cfg, W = bo.load_model(base_model)
+    ids, mask = bo.tokenize(vocab_path, sentences[:8], 128)
+    exact = bo.forward(cfg, W, ids, mask)
+    emu = bo.forward(cfg, W, ids, mask, emulate_bf16=True)
+    assert np.abs(exact - emu).max() < 2e-2
