@@ -282,6 +282,13 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     value = n * world / (ms_per_step / 1e3)
     launches_all = int(sum_over_ranks(float(launches)))
 
+    if args.profile_run:
+        if rank == 0:
+            print(json.dumps({"profile_run": True, "ms_per_step": ms_per_step, "items_per_s": value,
+                              "kernels": kern}), flush=True)
+        eng.close()
+        return
+
     # ---- e2e: C-ABI host call, pinned host buffers, H2D + D2H inside the timed region -------------
     eng.set_profiling(False)
     pin = []
@@ -409,6 +416,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--items", type=int, default=8192, help="items per GPU per step")
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--profile-run", action="store_true",
+                    help="short run for ncu: skip the e2e, op and CPU-baseline legs (the line is then not a bench value)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
