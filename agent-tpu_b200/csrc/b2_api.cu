@@ -911,3 +911,110 @@ int b2_chunk_bounds(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, i
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// b2_tokenize_noalloc — tokenize without allocating device memory
+// ================================================================================================
+// b2_tokenize stages the caller's host text on the device in buffers it grows with cudaMalloc when a
+// job is larger than the last one. Some callers must not trigger that: a worker whose memory budget
+// was handed out at start-up and who may not take more from the driver later, or a latency-bound
+// loop that cannot afford the device-wide synchronisation an allocation or free implies. For them
+// the staging area below is part of the library image instead: a fixed block of device memory that
+// exists on every GPU from the moment the library is loaded there until the process exits, whether
+// or not this entry point is ever called.
+//
+// Rules that follow from sharing one fixed block:
+//   * a job whose text, offsets, ids and mask do not fit in B2_NOALLOC_SCRATCH_BYTES is refused;
+//   * the block keeps whatever the previous call left in it, so the output region is cleared
+//     before the kernel runs;
+//   * two calls that overlap in time on the same GPU (different handles, different threads) would
+//     write the same bytes — callers must serialise them;
+//   * the first call on each GPU looks up the block's device address (a one-off set-up step);
+//     make that first call outside any stream capture.
+static __device__ __align__(256) uint8_t g_noalloc_scratch[B2_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+std::mutex g_noalloc_mu;
+uint8_t* g_noalloc_ptr[64] = {};  // per device: address of g_noalloc_scratch on that device
+
+// `g_noalloc_scratch` in host code is only a handle for the runtime, not an address a kernel can
+// use; the device address has to be asked for, once per device, with that device current.
+int noalloc_scratch_for(int device, uint8_t** out) {
+  if (device < 0 || device >= 64) {
+    set_last_error("b2_tokenize_noalloc: device ordinal %d is out of range", device);
+    return B2_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);  // caller made `device` current
+    if (e != cudaSuccess || !p) {
+      set_last_error("b2_tokenize_noalloc: cudaGetSymbolAddress failed on device %d: %s", device,
+                     cudaGetErrorString(e));
+      return B2_ERR_CUDA;
+    }
+    g_noalloc_ptr[device] = static_cast<uint8_t*>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return B2_OK;
+}
+
+inline size_t up256(size_t v) { return (v + 255) & ~size_t(255); }
+
+}  // namespace
+
+extern "C" int b2_tokenize_noalloc(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                                   int32_t max_len, int32_t* ids, uint8_t* mask) {
+  if (!h || !offsets || (n > 0 && !ids)) {
+    set_last_error("b2_tokenize_noalloc: NULL handle, offsets or ids");
+    return B2_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  if (!h->has_tokenizer) {
+    set_last_error("this handle was created without a tokenizer (b2_config.vocab_path was NULL)");
+    return B2_ERR_ARG;
+  }
+  if (max_len < 2 || n < 0 || n > 0x7fffffff) {
+    set_last_error("b2_tokenize_noalloc: need max_len >= 2 and 0 <= n < 2^31");
+    return B2_ERR_ARG;
+  }
+  const int64_t bytes = offsets[n];
+  if (offsets[0] != 0 || bytes < 0 || (bytes > 0 && !utf8)) {
+    set_last_error("b2_tokenize_noalloc: offsets must start at 0 and utf8 must not be NULL");
+    return B2_ERR_ARG;
+  }
+  // layout of the fixed block: text | offsets | ids | mask, each part 256-byte aligned
+  const size_t off_text = 0;
+  const size_t off_offs = off_text + up256(static_cast<size_t>(bytes) + 16);
+  const size_t off_ids = off_offs + up256(static_cast<size_t>(n + 1) * 8);
+  const size_t off_mask = off_ids + up256(static_cast<size_t>(n) * max_len * 4);
+  const size_t total = off_mask + up256(static_cast<size_t>(n) * max_len);
+  if (total > B2_NOALLOC_SCRATCH_BYTES) {
+    set_last_error("b2_tokenize_noalloc: job needs %zu bytes of staging (%lld text bytes, %lld items x "
+                   "max_len %d) but the fixed block holds %d; split the job or use b2_tokenize",
+                   total, (long long)bytes, (long long)n, max_len, B2_NOALLOC_SCRATCH_BYTES);
+    return B2_ERR_LIMIT;
+  }
+  uint8_t* base = nullptr;
+  int rc = noalloc_scratch_for(h->device, &base);
+  if (rc) return rc;
+  if (n == 0) return B2_OK;
+  uint8_t* d_text = base + off_text;
+  int64_t* d_offs = reinterpret_cast<int64_t*>(base + off_offs);
+  int32_t* d_ids = reinterpret_cast<int32_t*>(base + off_ids);
+  uint8_t* d_mask = base + off_mask;
+  cudaStream_t st = h->stream;
+  if (bytes) B2_CUDA_OK(cudaMemcpyAsync(d_text, utf8, bytes, cudaMemcpyHostToDevice, st));
+  B2_CUDA_OK(cudaMemcpyAsync(d_offs, offsets, static_cast<size_t>(n + 1) * 8, cudaMemcpyHostToDevice, st));
+  // the block still holds the previous call's rows: start the output region from zero
+  B2_CUDA_OK(cudaMemsetAsync(base + off_ids, 0, total - off_ids, st));
+  if ((rc = tokenizer_run(st, h->tok, d_text, d_offs, static_cast<int>(n), max_len, d_ids, d_mask, nullptr,
+                          h->num_sms))) return rc;
+  B2_CUDA_OK(cudaMemcpyAsync(ids, d_ids, static_cast<size_t>(n) * max_len * 4, cudaMemcpyDeviceToHost, st));
+  if (mask) B2_CUDA_OK(cudaMemcpyAsync(mask, d_mask, static_cast<size_t>(n) * max_len, cudaMemcpyDeviceToHost, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}

@@ -136,6 +136,22 @@ int b2_chunk_count(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, in
 int b2_chunk_bounds(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
                     int64_t chunk_size, const int64_t* chunk_base, int64_t n_chunks, int64_t* bounds);
 
+/* Tokenize-and-pad like b2_tokenize, but without allocating device memory during the call.
+ * No counterpart in the reference. It exists for callers that are not allowed to ask the CUDA
+ * driver for memory once they are running (a worker with a fixed memory budget, a loop that cannot
+ * absorb the synchronisation an allocation or free brings): the device-side staging for the text,
+ * offsets, ids and mask is a fixed block of B2_NOALLOC_SCRATCH_BYTES that every GPU holds from the
+ * moment the library is loaded there until exit.
+ *   - a job that does not fit the block (text bytes + 8*(n+1) + 5*n*max_len, each part rounded up
+ *     to 256) is refused with B2_ERR_LIMIT; b2_tokenize has no such limit;
+ *   - all calls on one GPU share the block: do not let two of them overlap in time, whichever
+ *     handles or threads they come from;
+ *   - the first call on each GPU looks up the block's address; make it before any stream capture.
+ * Host pointers; ids [n, max_len] int32; mask [n, max_len] uint8 or NULL. */
+#define B2_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
+int b2_tokenize_noalloc(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
+                        int32_t max_len, int32_t* ids, uint8_t* mask);
+
 #ifdef __cplusplus
 }
 #endif
