@@ -208,24 +208,32 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
 
-// erf with |abs error| < 1.5e-7 (Abramowitz & Stegun 7.1.26): one exp, one reciprocal, five FMAs.
-// Far below the bf16 rounding applied to the result; libdevice erff costs ~3x more issue slots in
-// the FFN1 epilogue, which would make that epilogue the pacing stage of the GEMM.
-__device__ __forceinline__ float fast_erf(float x) {
-  float ax = fabsf(x);
-  float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  p *= t;
-  float e = __expf(-ax * ax);
-  float r = fmaf(-p, e, 1.0f);
-  return copysignf(r, x);
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
 }
-// BERT's "gelu": x * 0.5 * (1 + erf(x / sqrt(2)))   (transformers activations.GELUActivation)
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// BERT's "gelu": x * Phi(x), Phi(x) = 0.5 * (1 + erf(x / sqrt(2)))  (transformers GELUActivation).
+// Phi(-|x|) = 0.5 * erfc(|x|/sqrt(2)) by Abramowitz & Stegun 7.1.26 (|abs error| < 1.5e-7 on erf):
+// one MUFU.RCP, one MUFU.EX2, nine FP32 ops — no slow paths, no branches. libdevice erff (and the
+// IEEE __frcp_rn the first version used) compile to call/branch sequences that left the FFN1
+// epilogue latency-bound at 23% tensor-pipe activity (profiles/r01_ncu_gemm.md).
 __device__ __forceinline__ float gelu_erf(float x) {
-  return 0.5f * x * (1.0f + fast_erf(x * 0.70710678118654752f));
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = rcp_approx(fmaf(0.3275911f, z, 1.0f));
+  float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);  // coefficients pre-halved
+  p = fmaf(p, t, 0.5f * 1.421413741f);
+  p = fmaf(p, t, 0.5f * -0.284496736f);
+  p = fmaf(p, t, 0.5f * 0.254829592f);
+  const float e = ex2_approx(z * z * -1.4426950408889634f);
+  const float h = p * t * e;                 // Phi(-|x|)
+  const float phi = x >= 0.f ? 1.0f - h : h;
+  return x * phi;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -11,8 +11,11 @@
 //   (48 KiB / stage), one tcgen05.mma of 128x256x16 per K=16, f32 accumulators in TMEM,
 //   two accumulator stages (2 x 256 columns = all 512 TMEM columns) so the epilogue of tile i
 //   overlaps the main loop of tile i+1.
-// Warp roles (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
-//   warp 3 idle, warps 4..11 = epilogue (TMEM lane quadrant = warp % 4, column half = (warp-4)/4).
+// Warp roles (640 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
+//   warp 3 idle, warps 4..19 = epilogue (TMEM lane quadrant = warp % 4, 64-column quarter =
+//   (warp-4)/4). Sixteen epilogue warps (four per SM sub-partition) because the epilogue is a chain
+//   of dependent FP32/MUFU operations per element: with two warps per sub-partition it ran at 0.35
+//   IPC and paced the FFN1 GEMM (profiles/r01_ncu_gemm.md).
 #include "b2_kernels.h"
 
 namespace b2 {
@@ -23,7 +26,8 @@ constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;
 constexpr int STAGES = 4;
-constexpr int THREADS = 384;
+constexpr int THREADS = 640;
+constexpr int EPI_WARPS = 16;
 constexpr uint32_t A_BYTES = BM * BK * 2;  // 16 KiB
 constexpr uint32_t B_BYTES = BN * BK * 2;  // 32 KiB
 constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
@@ -76,7 +80,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 8);  // one arrive per epilogue warp
+      mbar_init(tempty_bar(a), EPI_WARPS);  // one arrive per epilogue warp
     }
     fence_barrier_init();
   }
@@ -133,31 +137,39 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   } else if (warp >= 4) {
     // ===== epilogue: TMEM -> registers -> bias / activation / residual -> bf16 -> global =====
-    const int q = warp & 3;            // TMEM lane quadrant this warp may read
-    const int half = (warp - 4) >> 2;  // column half of the 256-wide tile
+    const int q = warp & 3;               // TMEM lane quadrant this warp may read
+    const int quarter = (warp - 4) >> 2;  // 64-column quarter of the 256-wide tile
     int it = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
       const int m_blk = t / n_tiles, n_blk = t % n_tiles;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
-      mbar_wait(tfull_bar(as), aphase);
-      tc_fence_after();
       const int row = m_blk * BM + q * 32 + lane;
       const bool row_ok = row < M;
+      const int colq = n_blk * BN + quarter * 64;
       __nv_bfloat16* crow = C + static_cast<size_t>(row) * ldc;
-      const __nv_bfloat16* rrow =
-          (EPI == GEMM_EPI_BIAS_RESIDUAL) ? residual + static_cast<size_t>(row) * ldr : nullptr;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        const int col0 = n_blk * BN + half * 128 + c * 32;
+      // the residual row segment does not depend on the accumulator: fetch it before waiting
+      uint4 res[8];
+      if (EPI == GEMM_EPI_BIAS_RESIDUAL) {
+        const __nv_bfloat16* rrow = residual + static_cast<size_t>(row) * ldr;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int col = colq + j * 8;
+          res[j] = (row_ok && col < N) ? __ldg(reinterpret_cast<const uint4*>(rrow + col))
+                                       : make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + quarter * 64;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + half * 128 +
-                          c * 32,
-                      r);
+        tmem_ld_32x32(tbase + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const int col = col0 + j * 8;
+          const int col = colq + c * 32 + j * 8;
           if (row_ok && col < N) {
             const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + col));
             const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + col + 4));
@@ -171,7 +183,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
             v[6] = __uint_as_float(r[j * 8 + 6]) + b1.z;
             v[7] = __uint_as_float(r[j * 8 + 7]) + b1.w;
             if (EPI == GEMM_EPI_BIAS_RESIDUAL) {
-              const uint4 rv = __ldg(reinterpret_cast<const uint4*>(rrow + col));
+              const uint4 rv = res[c * 4 + j];
               v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x);
               v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
               v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z);
