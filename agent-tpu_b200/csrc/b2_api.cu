@@ -125,6 +125,12 @@ struct b2_handle {
   CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{}, tm_att{};
   unsigned long long* hist = nullptr;
   int64_t* d_tokens = nullptr;  // running sum of lens
+  // packed (padding-free) layout: token rows of a batch are stored back to back, sequence b at
+  // rows [cu[b], cu[b+1]); cu[B] is the batch's row count, read by the kernels from device memory
+  bool packed = true;
+  int32_t* cu = nullptr;
+  __nv_bfloat16* cls = nullptr;  // [max_batch, H] gathered [CLS] rows
+  CUtensorMap tm_cls{};
 
   // growable staging for host-pointer calls
   uint8_t* st_text = nullptr; size_t st_text_cap = 0;
@@ -327,6 +333,10 @@ int alloc_activations(b2_handle* h) {
   if ((rc = A(reinterpret_cast<void**>(&h->ffn), rows * I * 2))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->pooled), int64_t(h->max_batch) * H * 2))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->hist), int64_t(m.num_labels) * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->cu), (int64_t(h->max_batch) + 1) * 4))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->cls), int64_t(h->max_batch) * H * 2))) return rc;
+  B2_CUDA_OK(cudaMemsetAsync(h->cls, 0, int64_t(h->max_batch) * H * 2, h->stream));
+  if ((rc = gemm_tmap_a(&h->tm_cls, h->cls, h->max_batch, H, H))) return rc;
   // pad rows are read by TMA boxes and attention tiles before they are ever written: give them
   // finite contents once so no NaN bit pattern can reach a masked-out product
   B2_CUDA_OK(cudaMemsetAsync(h->x, 0, rows * H * 2, h->stream));
@@ -369,38 +379,53 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
   const int H = m.hidden, I = m.intermediate, M = B * S;
   cudaStream_t st = h->stream;
   int rc;
+  // packed layout: M is only the upper bound; the kernels read the true row count from cu[B]
+  const int32_t* cu = h->packed ? h->cu : nullptr;
+  const int32_t* m_dev = h->packed ? h->cu + B : nullptr;
   mark(h, K_EMBED);
+  if (h->packed) {
+    if ((rc = pack_offsets(st, h->lens, B, h->cu))) return rc;
+    ++*launches;
+  }
   if ((rc = embed_layernorm(st, h->ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, h->x,
-                            M, S, H, m.vocab_size))) return rc;
+                            M, S, H, m.vocab_size, h->packed ? h->lens : nullptr, cu))) return rc;
   ++*launches;
   for (uint32_t l = 0; l < m.layers; ++l) {
     LayerWeights& L = h->layers[l];
     mark(h, K_GEMM_QKV);
     if ((rc = gemm_bf16_tn(st, h->tm_x, L.tm_qkv, h->qkv, L.bqkv, nullptr, M, 3 * H, H, 3 * H, 0,
-                           GEMM_EPI_BIAS, h->num_sms))) return rc;
+                           GEMM_EPI_BIAS, h->num_sms, m_dev))) return rc;
     mark(h, K_ATTENTION);
-    if ((rc = attention_bf16(st, h->tm_att, h->ctx, h->lens, B, S, H))) return rc;
+    if ((rc = attention_bf16(st, h->tm_att, h->ctx, h->lens, B, S, H, cu))) return rc;
     mark(h, K_GEMM_OUT);
     if ((rc = gemm_bf16_tn(st, h->tm_ctx, L.tm_o, h->y, L.bo, h->x, M, H, H, H, H,
-                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
+                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms, m_dev))) return rc;
     mark(h, K_LAYERNORM);
-    if ((rc = layernorm_inplace(st, h->y, L.ln1_g, L.ln1_b, m.ln_eps, M, H))) return rc;
+    if ((rc = layernorm_inplace(st, h->y, L.ln1_g, L.ln1_b, m.ln_eps, M, H, m_dev))) return rc;
     mark(h, K_GEMM_FFN1);
     if ((rc = gemm_bf16_tn(st, h->tm_y, L.tm_1, h->ffn, L.b1, nullptr, M, I, H, I, 0,
-                           GEMM_EPI_BIAS_GELU, h->num_sms))) return rc;
+                           GEMM_EPI_BIAS_GELU, h->num_sms, m_dev))) return rc;
     mark(h, K_GEMM_FFN2);
     if ((rc = gemm_bf16_tn(st, h->tm_ffn, L.tm_2, h->x, L.b2, h->y, M, H, I, H, H,
-                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
+                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms, m_dev))) return rc;
     mark(h, K_LAYERNORM);
-    if ((rc = layernorm_inplace(st, h->x, L.ln2_g, L.ln2_b, m.ln_eps, M, H))) return rc;
+    if ((rc = layernorm_inplace(st, h->x, L.ln2_g, L.ln2_b, m.ln_eps, M, H, m_dev))) return rc;
     *launches += 7;
   }
-  // pooler over the [CLS] rows: a strided view of x (row pitch S*H) through the A tensor map
-  CUtensorMap tm_cls;
-  if ((rc = gemm_tmap_a(&tm_cls, h->x, B, H, int64_t(S) * H))) return rc;
   mark(h, K_POOLER);
-  if ((rc = gemm_bf16_tn(st, tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
-                         GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
+  if (h->packed) {
+    // pooler over the [CLS] rows: row cu[b] of every sequence, gathered into a dense [B, H] block
+    if ((rc = gather_cls_rows(st, h->x, h->cu, B, H, h->cls))) return rc;
+    ++*launches;
+    if ((rc = gemm_bf16_tn(st, h->tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
+                           GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
+  } else {
+    // padded layout: the [CLS] rows are a strided view of x (row pitch S*H) through the A tensor map
+    CUtensorMap tm_cls;
+    if ((rc = gemm_tmap_a(&tm_cls, h->x, B, H, int64_t(S) * H))) return rc;
+    if ((rc = gemm_bf16_tn(st, tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
+                           GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
+  }
   mark(h, K_HEAD);
   if ((rc = classify_head(st, h->pooled, H, h->Wc, h->bc, B, H, m.num_labels, topk, d_logits,
                           d_top_idx, d_top_score, d_labels, h->hist))) return rc;
@@ -599,6 +624,15 @@ int b2_create(const b2_config* cfg, b2_handle** out) {
   h->num_sms = prop.multiProcessorCount;
   h->max_batch = cfg->max_batch > 0 ? cfg->max_batch : 1024;
   h->max_len = cfg->max_len > 0 ? cfg->max_len : 128;
+  // B2_FORCE_PADDED=1 keeps every sequence at max_len rows (the layout the packed path is tested
+  // against); the default stores only real tokens
+  const char* padded_env = getenv("B2_FORCE_PADDED");
+  h->packed = !(padded_env && padded_env[0] == '1');
+  if (h->max_batch > 4096) {
+    set_last_error("b2_create: max_batch %d exceeds 4096", h->max_batch);
+    delete h;
+    return B2_ERR_LIMIT;
+  }
   int rc = B2_OK;
   do {
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -653,6 +687,7 @@ int b2_get_model_info(b2_handle* h, b2_model_info* out) {
   out->max_batch = h->max_batch; out->max_len = h->max_len; out->device = h->device;
   out->sm_count = h->num_sms;
   out->weight_bytes = h->weight_bytes; out->activation_bytes = h->activation_bytes;
+  out->packed_rows = h->packed ? 1 : 0;
   return B2_OK;
 }
 

@@ -27,7 +27,8 @@ constexpr uint32_t ATT_SMEM = 1024 + 3 * TILE_BYTES + 2 * TILE_BYTES + 64;
 
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out,
-                 const int32_t* __restrict__ lens, int S, int hidden, int heads, int qblocks) {
+                 const int32_t* __restrict__ lens, int S, int hidden, int heads, int qblocks,
+                 const int32_t* __restrict__ cu) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -52,7 +53,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
   int len = lens[b];
   len = len < 0 ? 0 : (len > S ? S : len);
   const int nkb = (len + KB - 1) / KB;
-  const int row0 = b * S;  // first token row of this sequence
+  const int row0 = cu ? cu[b] : b * S;  // first token row of this sequence (packed or padded)
+  if (qb * QB >= len) return;           // query block of pad rows only: nothing to compute or store
 
   if (threadIdx.x == 128) {
     tma_prefetch_desc(&tmap_qkv);
@@ -177,7 +179,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
       }
     }
     const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+    // rows past the sequence's length are pad (padded layout) or belong to the next sequence
+    // (packed layout): never written
     __nv_bfloat16* dst = out + static_cast<size_t>(row0 + qb * QB + r) * hidden + h * HD;
+    if (qb * QB + r < len)
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       uint4 w;
@@ -205,7 +210,7 @@ int attention_tmap_qkv(CUtensorMap* out, const void* qkv, int rows, int hidden) 
 }
 
 int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* out,
-                   const int32_t* lens, int B, int S, int hidden) {
+                   const int32_t* lens, int B, int S, int hidden, const int32_t* cu) {
   if (B <= 0 || S <= 0 || (S % QB) != 0 || hidden <= 0 || (hidden % HD) != 0) {
     set_last_error("attention_bf16: needs S %% 128 == 0 and hidden %% 64 == 0 (got S=%d hidden=%d)", S,
                    hidden);
@@ -226,7 +231,7 @@ int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* 
     return B2_ERR_ARG;
   }
   attention_kernel<<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM, stream>>>(
-      tqkv, out, lens, S, hidden, heads, qblocks);
+      tqkv, out, lens, S, hidden, heads, qblocks, cu);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }

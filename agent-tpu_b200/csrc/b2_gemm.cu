@@ -46,8 +46,11 @@ __global__ void __launch_bounds__(THREADS, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b, __nv_bfloat16* __restrict__ C,
                     const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
-                    int M, int N, int K, int ldc, int ldr) {
+                    int M, int N, int K, int ldc, int ldr, const int32_t* __restrict__ m_dev) {
   extern __shared__ uint8_t smem_raw[];
+  // packed (padding-free) batches: the row count is produced on the device by the pack kernel, so
+  // the host never has to synchronise to learn it; `M` is then only the upper bound
+  if (m_dev) M = min(M, __ldg(m_dev));
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   const uint32_t sA = base;
@@ -217,7 +220,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
 template <int EPI>
 int launch(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, __nv_bfloat16* C,
            const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int ldc, int ldr,
-           int num_sms) {
+           int num_sms, const int32_t* m_dev) {
   static bool configured[64] = {};
   int dev = 0;
   B2_CUDA_OK(cudaGetDevice(&dev));
@@ -229,7 +232,7 @@ int launch(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, __
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms ? tiles : num_sms;
   gemm_bf16_tn_kernel<EPI><<<grid, THREADS, SMEM_BYTES, stream>>>(ta, tb, C, bias, residual, M, N,
-                                                                  K, ldc, ldr);
+                                                                  K, ldc, ldr, m_dev);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }
@@ -245,7 +248,7 @@ int gemm_tmap_b(CUtensorMap* out, const void* W, int N, int K) {
 
 int gemm_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb,
                  __nv_bfloat16* C, const float* bias, const __nv_bfloat16* residual, int M, int N,
-                 int K, int ldc, int ldr, int epilogue, int num_sms) {
+                 int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev) {
   if (M <= 0 || N <= 0 || K <= 0 || (N % 8) != 0 || (K % 8) != 0 || (ldc % 8) != 0) {
     set_last_error("gemm_bf16_tn: bad shape M=%d N=%d K=%d ldc=%d (N, K, ldc must be multiples of 8)",
                    M, N, K, ldc);
@@ -253,20 +256,20 @@ int gemm_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& 
   }
   switch (epilogue) {
     case GEMM_EPI_BIAS:
-      return launch<GEMM_EPI_BIAS>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms);
+      return launch<GEMM_EPI_BIAS>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms, m_dev);
     case GEMM_EPI_BIAS_GELU:
       return launch<GEMM_EPI_BIAS_GELU>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr,
-                                        num_sms);
+                                        num_sms, m_dev);
     case GEMM_EPI_BIAS_RESIDUAL:
       if (!residual || (ldr % 8) != 0) {
         set_last_error("gemm_bf16_tn: residual epilogue needs a residual pointer and ldr %% 8 == 0");
         return B2_ERR_ARG;
       }
       return launch<GEMM_EPI_BIAS_RESIDUAL>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr,
-                                            num_sms);
+                                            num_sms, m_dev);
     case GEMM_EPI_BIAS_TANH:
       return launch<GEMM_EPI_BIAS_TANH>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr,
-                                        num_sms);
+                                        num_sms, m_dev);
   }
   set_last_error("gemm_bf16_tn: unknown epilogue %d", epilogue);
   return B2_ERR_ARG;

@@ -15,25 +15,34 @@ enum GemmEpilogue {
 // Tensor maps: A is [M,K] bf16 with row pitch lda elements, W is [N,K] bf16 dense.
 int gemm_tmap_a(CUtensorMap* out, const void* A, int M, int K, int64_t lda);
 int gemm_tmap_b(CUtensorMap* out, const void* W, int N, int K);
+// m_dev (optional, device memory): actual row count, M is then an upper bound (packed batches).
 int gemm_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb,
                  __nv_bfloat16* C, const float* bias, const __nv_bfloat16* residual, int M, int N,
-                 int K, int ldc, int ldr, int epilogue, int num_sms);
+                 int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev = nullptr);
 
 // ---- attention (b2_attention.cu) ---------------------------------------------------------------
-// qkv: [B*S, 3*H] bf16 (Q | K | V per token row, head h at columns h*64), out: [B*S, H] bf16.
-// lens[b] = number of valid (unpadded) tokens of sequence b; keys >= lens[b] are masked out.
+// qkv: [rows, 3*H] bf16 (Q | K | V per token row, head h at columns h*64), out: [rows, H] bf16.
+// lens[b] = number of valid (unpadded) tokens of sequence b; keys >= lens[b] are masked out and
+// query rows >= lens[b] are not written. Sequence b starts at row cu[b] (packed) or b*S (cu null).
 int attention_tmap_qkv(CUtensorMap* out, const void* qkv, int rows, int hidden);
 int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* out,
-                   const int32_t* lens, int B, int S, int hidden);
+                   const int32_t* lens, int B, int S, int hidden, const int32_t* cu = nullptr);
 
 // ---- element-wise / row kernels (b2_rows.cu) ---------------------------------------------------
 // out[row] = LayerNorm(word[ids[row]] + pos[row % S] + type[0]) * gamma + beta  -> bf16
+// packed: with lens / cu given, token (b, s) is written to row cu[b] + s and pad positions are skipped.
 int embed_layernorm(cudaStream_t stream, const int32_t* ids, const float* word, const float* pos,
                     const float* type0, const float* gamma, const float* beta, float eps,
-                    __nv_bfloat16* out, int rows, int S, int hidden, int vocab);
+                    __nv_bfloat16* out, int rows, int S, int hidden, int vocab,
+                    const int32_t* lens = nullptr, const int32_t* cu = nullptr);
 // x[row] = LayerNorm(x[row]) * gamma + beta   (in place, bf16 storage, f32 math)
 int layernorm_inplace(cudaStream_t stream, __nv_bfloat16* x, const float* gamma, const float* beta,
-                      float eps, int rows, int hidden);
+                      float eps, int rows, int hidden, const int32_t* rows_dev = nullptr);
+// cu[0..B] = exclusive prefix sum of lens, cu[B] = total rows (also the GEMMs' m_dev); B <= 4096.
+int pack_offsets(cudaStream_t stream, const int32_t* lens, int B, int32_t* cu);
+// dst[b, :] = src[cu[b], :]   (the [CLS] row of every packed sequence)
+int gather_cls_rows(cudaStream_t stream, const __nv_bfloat16* src, const int32_t* cu, int B, int hidden,
+                    __nv_bfloat16* dst);
 // logits[b, c] = pooled[b,:] · Wc[c,:] + bc[c]; probs = softmax(logits); top-k (descending, ties
 // by lower index), label = argmax, histogram[label] += 1.
 int classify_head(cudaStream_t stream, const __nv_bfloat16* pooled, int ld_pooled, const float* Wc,

@@ -19,10 +19,17 @@ __global__ void __launch_bounds__(256)
 embed_ln_kernel(const int32_t* __restrict__ ids, const float* __restrict__ word,
                 const float* __restrict__ pos, const float* __restrict__ type0,
                 const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
-                __nv_bfloat16* __restrict__ out, int rows, int S, int hidden, int vocab) {
-  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+                __nv_bfloat16* __restrict__ out, int rows, int S, int hidden, int vocab,
+                const int32_t* __restrict__ lens, const int32_t* __restrict__ cu) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);  // padded position b*S + s
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
+  int out_row = row;
+  if (cu) {
+    const int b = row / S, sp = row - b * S;
+    if (sp >= lens[b]) return;  // pad position: no row in the packed layout
+    out_row = cu[b] + sp;
+  }
   int id = ids[row];
   id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
   const float* w = word + static_cast<size_t>(id) * hidden;
@@ -51,7 +58,7 @@ embed_ln_kernel(const int32_t* __restrict__ ids, const float* __restrict__ word,
     }
   }
   const float rstd = rsqrtf(warp_sum(sq) / hidden + eps);
-  __nv_bfloat16* o = out + static_cast<size_t>(row) * hidden;
+  __nv_bfloat16* o = out + static_cast<size_t>(out_row) * hidden;
 #pragma unroll
   for (int i = 0; i < MAX_VEC; ++i) {
     if (i < nvec) {
@@ -69,8 +76,10 @@ embed_ln_kernel(const int32_t* __restrict__ ids, const float* __restrict__ word,
 // ---- LayerNorm in place over bf16 rows ----------------------------------------------------------
 __global__ void __launch_bounds__(256)
 layernorm_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
-                 const float* __restrict__ beta, float eps, int rows, int hidden) {
+                 const float* __restrict__ beta, float eps, int rows, int hidden,
+                 const int32_t* __restrict__ rows_dev) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (rows_dev) rows = min(rows, __ldg(rows_dev));
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   __nv_bfloat16* xr = x + static_cast<size_t>(row) * hidden;
@@ -181,6 +190,55 @@ classify_head_kernel(const __nv_bfloat16* __restrict__ pooled, int ld_pooled,
   }
 }
 
+// exclusive prefix sum of lens[0..B) -> cu[0..B], one CTA of 1024 threads, up to 4 items per thread
+__global__ void __launch_bounds__(1024) pack_offsets_kernel(const int32_t* __restrict__ lens, int B,
+                                                            int32_t* __restrict__ cu) {
+  __shared__ int warp_tot[32];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  int v[4], sum = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int idx = t * 4 + i;
+    v[i] = idx < B ? lens[idx] : 0;
+    sum += v[i];
+  }
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int y = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += y;
+  }
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int w = warp_tot[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += y;
+    }
+    warp_tot[lane] = w;  // inclusive totals of warps 0..lane
+  }
+  __syncthreads();
+  int run = incl - sum + (warp > 0 ? warp_tot[warp - 1] : 0);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int idx = t * 4 + i;
+    if (idx < B) cu[idx] = run;
+    run += v[i];
+  }
+  if (t == 1023) cu[B] = warp_tot[31];
+}
+
+__global__ void gather_cls_kernel(const __nv_bfloat16* __restrict__ src, const int32_t* __restrict__ cu,
+                                  int B, int hidden, __nv_bfloat16* __restrict__ dst) {
+  const int b = blockIdx.x;
+  if (b >= B) return;
+  const uint2* s = reinterpret_cast<const uint2*>(src + static_cast<size_t>(cu[b]) * hidden);
+  uint2* d = reinterpret_cast<uint2*>(dst + static_cast<size_t>(b) * hidden);
+  for (int i = threadIdx.x; i < hidden / 4; i += blockDim.x) d[i] = s[i];
+}
+
 __global__ void mask_to_lens_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ lens,
                                     int B, int S) {
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -197,7 +255,8 @@ __global__ void mask_to_lens_kernel(const uint8_t* __restrict__ mask, int32_t* _
 
 int embed_layernorm(cudaStream_t stream, const int32_t* ids, const float* word, const float* pos,
                     const float* type0, const float* gamma, const float* beta, float eps,
-                    __nv_bfloat16* out, int rows, int S, int hidden, int vocab) {
+                    __nv_bfloat16* out, int rows, int S, int hidden, int vocab, const int32_t* lens,
+                    const int32_t* cu) {
   if ((hidden % 128) != 0 || hidden > MAX_VEC * 128) {
     set_last_error("embed_layernorm: hidden must be a multiple of 128 and <= %d", MAX_VEC * 128);
     return B2_ERR_ARG;
@@ -205,20 +264,21 @@ int embed_layernorm(cudaStream_t stream, const int32_t* ids, const float* word, 
   if (rows <= 0) return B2_OK;
   const int wpb = 8;
   embed_ln_kernel<<<(rows + wpb - 1) / wpb, wpb * 32, 0, stream>>>(ids, word, pos, type0, gamma, beta,
-                                                                  eps, out, rows, S, hidden, vocab);
+                                                                  eps, out, rows, S, hidden, vocab, lens, cu);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }
 
 int layernorm_inplace(cudaStream_t stream, __nv_bfloat16* x, const float* gamma, const float* beta,
-                      float eps, int rows, int hidden) {
+                      float eps, int rows, int hidden, const int32_t* rows_dev) {
   if ((hidden % 128) != 0 || hidden > MAX_VEC * 128) {
     set_last_error("layernorm_inplace: hidden must be a multiple of 128 and <= %d", MAX_VEC * 128);
     return B2_ERR_ARG;
   }
   if (rows <= 0) return B2_OK;
   const int wpb = 8;
-  layernorm_kernel<<<(rows + wpb - 1) / wpb, wpb * 32, 0, stream>>>(x, gamma, beta, eps, rows, hidden);
+  layernorm_kernel<<<(rows + wpb - 1) / wpb, wpb * 32, 0, stream>>>(x, gamma, beta, eps, rows, hidden,
+                                                                   rows_dev);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }
@@ -236,6 +296,24 @@ int classify_head(cudaStream_t stream, const __nv_bfloat16* pooled, int ld_poole
   const size_t smem = static_cast<size_t>(HEAD_WARPS) * C * sizeof(float);
   classify_head_kernel<<<(B + HEAD_WARPS - 1) / HEAD_WARPS, HEAD_WARPS * 32, smem, stream>>>(
       pooled, ld_pooled, Wc, bc, B, hidden, C, topk, logits, top_idx, top_score, labels, histogram);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int pack_offsets(cudaStream_t stream, const int32_t* lens, int B, int32_t* cu) {
+  if (B < 0 || B > 4096) {
+    set_last_error("pack_offsets: batch of %d sequences exceeds 4096", B);
+    return B2_ERR_LIMIT;
+  }
+  pack_offsets_kernel<<<1, 1024, 0, stream>>>(lens, B, cu);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int gather_cls_rows(cudaStream_t stream, const __nv_bfloat16* src, const int32_t* cu, int B, int hidden,
+                    __nv_bfloat16* dst) {
+  if (B <= 0) return B2_OK;
+  gather_cls_kernel<<<B, 128, 0, stream>>>(src, cu, B, hidden, dst);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }

@@ -54,7 +54,8 @@ class ModelInfo(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("hidden", "layers", "heads", "intermediate", "vocab_size",
                                          "max_positions", "num_labels", "tokenizer_vocab_size",
                                          "max_batch", "max_len", "device", "sm_count")] + \
-               [("weight_bytes", C.c_int64), ("activation_bytes", C.c_int64)]
+               [("weight_bytes", C.c_int64), ("activation_bytes", C.c_int64), ("packed_rows", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 _METRIC_KINDS = ("tokenize", "embed", "gemm_qkv", "attention", "gemm_attn_out", "layernorm", "gemm_ffn1",

@@ -49,6 +49,8 @@ typedef struct b2_model_info {
   int32_t vocab_size, max_positions, num_labels, tokenizer_vocab_size;
   int32_t max_batch, max_len, device, sm_count;
   int64_t weight_bytes, activation_bytes;
+  int32_t packed_rows; /* 1: padding-free token rows (default); 0: B2_FORCE_PADDED=1 was set */
+  int32_t reserved;
 } b2_model_info;
 
 /* Per-call counters and device timings (CUDA events on the library's stream). The reference

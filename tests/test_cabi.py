@@ -36,7 +36,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_sizes_match_the_header():
     # b2_config: 2 x i32, 3 pointers, 2 x i32 ; b2_model_info: 12 x i32 + 2 x i64
     assert C.sizeof(rt._Config) == 8 + 3 * C.sizeof(C.c_void_p) + 8
-    assert C.sizeof(rt.ModelInfo) == 12 * 4 + 16
+    assert C.sizeof(rt.ModelInfo) == 12 * 4 + 16 + 8
     assert C.sizeof(rt.Metrics) == 8 + 7 * 8 + 8 + 10 * 8 + 10 * 8
     assert C.sizeof(rt.DeviceInfo) == 128 + 8 + 16
 

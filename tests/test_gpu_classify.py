@@ -120,6 +120,25 @@ def test_batch_size_and_order_independence(tiny_model, vocab_path, sentences):
         a.close(); b.close()
 
 
+def test_packed_rows_equal_padded_rows_bit_for_bit(tiny_model, vocab_path, sentences, monkeypatch):
+    """Padding-free token rows (default) against B2_FORCE_PADDED=1: same logits to the last bit."""
+    from ops import _cuda_runtime as rt
+    texts = sentences[:100] + ["", "x"] + sentences[100:140]
+    a = rt.Engine(tiny_model, vocab_path, max_batch=48, max_len=512)
+    monkeypatch.setenv("B2_FORCE_PADDED", "1")
+    b = rt.Engine(tiny_model, vocab_path, max_batch=48, max_len=512)
+    monkeypatch.delenv("B2_FORCE_PADDED")
+    try:
+        assert a.info.packed_rows == 1 and b.info.packed_rows == 0
+        for ml in (128, 512):
+            oa = a.classify(texts, ml, 3, want_logits=True)
+            ob = b.classify(texts, ml, 3, want_logits=True)
+            assert (oa["logits"] == ob["logits"]).all() and (oa["top_idx"] == ob["top_idx"]).all()
+            assert (oa["histogram"] == ob["histogram"]).all()
+    finally:
+        a.close(); b.close()
+
+
 def test_ids_entry_point_equals_text_entry_point(tiny_engine, sentences):
     texts = sentences[:70]
     ids, mask, _ = tiny_engine.tokenize(texts, 128)
@@ -155,7 +174,10 @@ def test_full_batch_job_properties(base_engine, sentences):
     assert (out["top_score"][:n] == out["top_score"][2 * n:3 * n]).all()
     m = out["metrics"]
     assert m["batches"] == 8 and m["items"] == 8192
+    # timed segments per batch: tokenize, embed, 12 x 7 layer kernels, pooler, head
     assert sum(v["launches"] for v in m["kernels"].values()) == 8 * (1 + 1 + 12 * 7 + 2)
+    extra = 2 if base_engine.info.packed_rows else 0      # pack offsets + [CLS] gather
+    assert m["kernel_launches"] == 8 * (1 + 1 + 1 + 12 * 7 + 2 + extra) + 1   # + lens sum, + histogram copy
     assert 0 < sum(v["ms"] for v in m["kernels"].values()) <= m["gpu_ms_total"] * 1.05
 
 
