@@ -122,7 +122,8 @@ struct b2_handle {
   uint8_t* mask = nullptr;
   __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *ffn = nullptr,
                 *pooled = nullptr;
-  CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{}, tm_att{};
+  CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{};
+  AttentionMaps tm_att{};
   unsigned long long* hist = nullptr;
   int64_t* d_tokens = nullptr;  // running sum of lens
   // packed (padding-free) layout: token rows of a batch are stored back to back, sequence b at
@@ -348,7 +349,7 @@ int alloc_activations(b2_handle* h) {
   if ((rc = gemm_tmap_a(&h->tm_ctx, h->ctx, rows, H, H))) return rc;
   if ((rc = gemm_tmap_a(&h->tm_y, h->y, rows, H, H))) return rc;
   if ((rc = gemm_tmap_a(&h->tm_ffn, h->ffn, rows, I, I))) return rc;
-  if ((rc = attention_tmap_qkv(&h->tm_att, h->qkv, rows, H))) return rc;
+  if ((rc = attention_tmaps(&h->tm_att, h->qkv, rows, H))) return rc;
   B2_CUDA_OK(cudaStreamSynchronize(h->stream));
   return B2_OK;
 }

@@ -1,13 +1,21 @@
 // b2_attention.cu — masked self-attention for the encoder, head dim 64, on tcgen05 + TMA.
 //
 // One CTA handles one (sequence, head, 128-query block). For each 128-key block it runs
-//   S = Q·Kᵀ            tcgen05.mma 128x128x64   (Q, K: K-major 128-byte-swizzled TMA tiles)
+//   S = Q·Kᵀ            tcgen05.mma 128 x n x 64  (Q, K: K-major 128-byte-swizzled TMA tiles)
 //   P = exp2((S-m)·c)    one thread per query row, S read from TMEM, keys >= len masked out
-//   O_blk = P·V          tcgen05.mma 128x64x128   (P: written to swizzled smem as the A operand,
+//   O_blk = P·V          tcgen05.mma 128 x 64 x n  (P: written to swizzled smem as the A operand,
 //                                                  V: MN-major TMA tile, no transpose needed)
-// and folds O_blk into a running, rescaled f32 accumulator held in registers (online softmax), so
-// S = 128 is one pass and S = 512 is four. Key blocks that lie wholly beyond the sequence's length
-// are never loaded.
+// with n = the block's valid keys rounded up to 32: the TMA boxes (four tensor maps with 32, 64, 96
+// and 128 rows), the UMMA N of Q·Kᵀ and the K extent of P·V all shrink with the sequence, so a
+// 40-token sentence moves and multiplies a third of what a 128-token one does. Rows of the tiles
+// beyond the box hold stale shared memory; they are never read by an MMA whose result is kept.
+//
+// Two instantiations:
+//   SINGLE (S <= 128): one key block. P overlays the Q|K tiles (dead once Q·Kᵀ has completed) and
+//     O overlays S in TMEM, so a CTA needs 48 KiB of smem and 128 TMEM columns: 4 CTAs per SM
+//     overlap each other's load -> MMA -> softmax -> MMA -> store chains.
+//   MULTI (S = 256..512): online softmax over key blocks, running f32 output in registers; key
+//     blocks and query blocks wholly beyond the sequence's length are skipped.
 //
 // No reference counterpart: the reference's model is an opaque TFLite graph
 // (ops/map_classify_tpu.py:71-72). Semantics follow BertSelfAttention (scores/sqrt(d) + additive
@@ -23,10 +31,16 @@ constexpr int QB = 128;           // queries per CTA
 constexpr int KB = 128;           // keys per block
 constexpr int HD = 64;            // head dim
 constexpr uint32_t TILE_BYTES = 128 * 64 * 2;  // 16 KiB: a [128 x 64] bf16 tile
-constexpr uint32_t ATT_SMEM = 1024 + 3 * TILE_BYTES + 2 * TILE_BYTES + 64;
+constexpr uint32_t ATT_SMEM_SINGLE = 1024 + 3 * TILE_BYTES + 64;
+constexpr uint32_t ATT_SMEM_MULTI = 1024 + 5 * TILE_BYTES + 64;
 
-__global__ void __launch_bounds__(ATT_THREADS, 2)
-attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out,
+struct AttMaps {
+  CUtensorMap m[4];  // box rows 32, 64, 96, 128 over the same [rows, 3H] buffer
+};
+
+template <bool SINGLE>
+__global__ void __launch_bounds__(ATT_THREADS, SINGLE ? 4 : 2)
+attention_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
                  const int32_t* __restrict__ lens, int S, int hidden, int heads, int qblocks,
                  const int32_t* __restrict__ cu) {
   extern __shared__ uint8_t smem_raw[];
@@ -35,8 +49,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
   const uint32_t sQ = base;
   const uint32_t sK = base + TILE_BYTES;
   const uint32_t sV = base + 2 * TILE_BYTES;
-  const uint32_t sP = base + 3 * TILE_BYTES;  // two [128 x 64] K-major tiles (keys 0-63, 64-127)
-  const uint32_t bars = base + 5 * TILE_BYTES;
+  // P: two [128 x 64] K-major tiles (keys 0-63, 64-127)
+  constexpr uint32_t P_OFF = SINGLE ? 0u : 3 * TILE_BYTES;
+  const uint32_t sP = base + P_OFF;
+  const uint32_t bars = base + (SINGLE ? 3 : 5) * TILE_BYTES;
   const uint32_t q_full = bars, kv_full = bars + 8, s_full = bars + 16, p_full = bars + 24,
                  o_full = bars + 32, tmem_slot = bars + 40;
   uint8_t* smem_aligned = smem_raw + (base - raw);
@@ -55,9 +71,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
   const int nkb = (len + KB - 1) / KB;
   const int row0 = cu ? cu[b] : b * S;  // first token row of this sequence (packed or padded)
   if (qb * QB >= len) return;           // query block of pad rows only: nothing to compute or store
+  const int qvalid = min(QB, len - qb * QB);
+  constexpr uint32_t TMEM_COLS = SINGLE ? 128 : 256;
 
   if (threadIdx.x == 128) {
-    tma_prefetch_desc(&tmap_qkv);
     mbar_init(q_full, 1);
     mbar_init(kv_full, 1);
     mbar_init(s_full, 1);
@@ -65,29 +82,32 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
     mbar_init(o_full, 1);
     fence_barrier_init();
   }
-  if (warp == 4) tmem_alloc<256>(tmem_slot);
+  if (warp == 4) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
-  const uint32_t tmem_S = tmem_base;        // 128 columns
-  const uint32_t tmem_O = tmem_base + 128;  // 64 columns
+  const uint32_t tmem_S = tmem_base;                         // up to 128 columns
+  const uint32_t tmem_O = tmem_base + (SINGLE ? 0u : 128u);  // 64 columns (SINGLE: over S)
 
   if (warp == 4) {
-    if (lane == 0 && nkb > 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
-      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
-      mbar_expect_tx(q_full, TILE_BYTES);
-      tma_load_2d(sQ, &tmap_qkv, q_full, h * HD, row0 + qb * QB);
+    if (lane == 0) {
+      const int qbox = (qvalid + 31) >> 5;  // 1..4 -> 32..128 rows
+      mbar_expect_tx(q_full, qbox * 32 * 128);
+      tma_load_2d(sQ, &maps.m[qbox - 1], q_full, h * HD, row0 + qb * QB);
       for (int kb = 0; kb < nkb; ++kb) {
+        const int kvalid = min(KB, len - kb * KB);
+        const int kbox = (kvalid + 31) >> 5;
+        const int nk = kbox * 32;  // keys this block's MMAs cover
         if (kb > 0) mbar_wait(o_full, (kb - 1) & 1);  // P·V of the previous block has read K/V/P
-        mbar_expect_tx(kv_full, 2 * TILE_BYTES);
-        tma_load_2d(sK, &tmap_qkv, kv_full, hidden + h * HD, row0 + kb * KB);
-        tma_load_2d(sV, &tmap_qkv, kv_full, 2 * hidden + h * HD, row0 + kb * KB);
+        mbar_expect_tx(kv_full, 2 * nk * 128);
+        tma_load_2d(sK, &maps.m[kbox - 1], kv_full, hidden + h * HD, row0 + kb * KB);
+        tma_load_2d(sV, &maps.m[kbox - 1], kv_full, 2 * hidden + h * HD, row0 + kb * KB);
         if (kb == 0) mbar_wait(q_full, 0);
         mbar_wait(kv_full, kb & 1);
         tc_fence_after();
         {
+          const uint32_t idesc_s = umma_idesc_bf16(128, nk, 0, 0);
           const uint64_t qd = umma_desc_sw128(sQ, 16, 1024);
           const uint64_t kd = umma_desc_sw128(sK, 16, 1024);
 #pragma unroll
@@ -96,8 +116,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
         umma_commit(s_full);
         mbar_wait(p_full, kb & 1);
         tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < KB / 16; ++k) {
+        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
+        for (int k = 0; k < nk / 16; ++k) {
           // A = P: K-major, 64 keys per 16 KiB tile, 32 bytes per K=16 step inside the swizzle atom
           const uint64_t pd = umma_desc_sw128(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
           // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes per step
@@ -113,9 +133,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
     const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
     const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
     float m_run = -INFINITY, l_run = 0.f;
-    float o[HD];
+    float o[SINGLE ? 1 : HD];
+    if (!SINGLE) {
 #pragma unroll
-    for (int i = 0; i < HD; ++i) o[i] = 0.f;
+      for (int i = 0; i < (SINGLE ? 1 : HD); ++i) o[i] = 0.f;
+    }
 
     for (int kb = 0; kb < nkb; ++kb) {
       mbar_wait(s_full, kb & 1);
@@ -132,12 +154,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
             if (c * 32 + j < kvalid) mx = fmaxf(mx, __uint_as_float(v[j]));
         }
       }
+      // rows of stale shared memory (beyond the Q box) may hold anything, NaN included; their
+      // results are never stored, they only must not disturb the arithmetic of this thread
       const float m_new = fmaxf(m_run, mx);
       const float alpha = exp2f((m_run - m_new) * sl2);
       float rowsum = 0.f;
       for (int c = 0; c < 4; ++c) {
-        uint32_t packed[16];
-        if (c * 32 < kvalid) {
+        if (c * 32 < kvalid) {  // chunks at or beyond the key box are never read by the P·V MMA
+          uint32_t packed[16];
           uint32_t v[32];
           tmem_ld_32x32(tmem_S + lane_base + c * 32, v);
           tmem_ld_wait();
@@ -148,17 +172,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
             rowsum += p0 + p1;
             packed[j >> 1] = pack_bf16x2(p0, p1);
           }
-        } else {
+          // (SINGLE: P lands on the Q|K tiles; safe, s_full is only signalled once Q·Kᵀ completed)
+          // keys [c*32, c*32+32) -> tile (c >> 1), 16-byte chunks ((c & 1) * 4 + j) ^ (r & 7)
+          uint8_t* tile = smem_aligned + P_OFF + (c >> 1) * TILE_BYTES + r * 128;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) packed[j] = 0u;
-        }
-        // keys [c*32, c*32+32) -> tile (c >> 1), 16-byte chunks ((c & 1) * 4 + j) ^ (r & 7)
-        uint8_t* tile = smem_aligned + 3 * TILE_BYTES + (c >> 1) * TILE_BYTES + r * 128;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
-          *reinterpret_cast<uint4*>(tile + chunk * 16) =
-              make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
+          for (int j = 0; j < 4; ++j) {
+            const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
+            *reinterpret_cast<uint4*>(tile + chunk * 16) =
+                make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
+          }
         }
       }
       l_run = l_run * alpha + rowsum;
@@ -169,28 +191,51 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
 
       mbar_wait(o_full, kb & 1);
       tc_fence_after();
+      if (!SINGLE) {
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_O + lane_base + c * 32, v);
-        tmem_ld_wait();
+        for (int c = 0; c < 2; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_O + lane_base + c * 32, v);
+          tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; ++j) o[c * 32 + j] = o[c * 32 + j] * alpha + __uint_as_float(v[j]);
+          for (int j = 0; j < 32; ++j)
+            o[(SINGLE ? 0 : c * 32 + j)] = o[(SINGLE ? 0 : c * 32 + j)] * alpha + __uint_as_float(v[j]);
+        }
       }
     }
     const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
     // rows past the sequence's length are pad (padded layout) or belong to the next sequence
     // (packed layout): never written
     __nv_bfloat16* dst = out + static_cast<size_t>(row0 + qb * QB + r) * hidden + h * HD;
-    if (qb * QB + r < len)
+    const bool store = r < qvalid;
+    if (SINGLE) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      uint4 w;
-      w.x = pack_bf16x2(o[j * 8 + 0] * inv, o[j * 8 + 1] * inv);
-      w.y = pack_bf16x2(o[j * 8 + 2] * inv, o[j * 8 + 3] * inv);
-      w.z = pack_bf16x2(o[j * 8 + 4] * inv, o[j * 8 + 5] * inv);
-      w.w = pack_bf16x2(o[j * 8 + 6] * inv, o[j * 8 + 7] * inv);
-      *reinterpret_cast<uint4*>(dst + j * 8) = w;
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_O + lane_base + c * 32, v);
+        tmem_ld_wait();
+        if (store) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 w;
+            w.x = pack_bf16x2(__uint_as_float(v[j * 8 + 0]) * inv, __uint_as_float(v[j * 8 + 1]) * inv);
+            w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
+            w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
+            w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + c * 32 + j * 8) = w;
+          }
+        }
+      }
+    } else if (store) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        uint4 w;
+        w.x = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 0)] * inv, o[(SINGLE ? 0 : j * 8 + 1)] * inv);
+        w.y = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 2)] * inv, o[(SINGLE ? 0 : j * 8 + 3)] * inv);
+        w.z = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 4)] * inv, o[(SINGLE ? 0 : j * 8 + 5)] * inv);
+        w.w = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 6)] * inv, o[(SINGLE ? 0 : j * 8 + 7)] * inv);
+        *reinterpret_cast<uint4*>(dst + j * 8) = w;
+      }
     }
   }
 
@@ -198,18 +243,25 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __
   __syncthreads();
   if (warp == 4) {
     tc_fence_after();
-    tmem_dealloc<256>(tmem_base);
+    tmem_dealloc<TMEM_COLS>(tmem_base);
   }
 }
 
 }  // namespace
 
-int attention_tmap_qkv(CUtensorMap* out, const void* qkv, int rows, int hidden) {
-  return make_tmap_bf16_2d(out, qkv, rows, 3 * hidden, static_cast<uint64_t>(3 * hidden) * 2, 128,
-                           64);
+// `out` holds four tensor maps (box rows 32, 64, 96, 128) packed into AttentionMaps::raw.
+int attention_tmaps(AttentionMaps* out, const void* qkv, int rows, int hidden) {
+  static_assert(sizeof(AttentionMaps) == sizeof(AttMaps), "AttentionMaps layout");
+  AttMaps* m = reinterpret_cast<AttMaps*>(out);
+  for (int i = 0; i < 4; ++i) {
+    int rc = make_tmap_bf16_2d(&m->m[i], qkv, rows, 3 * hidden, static_cast<uint64_t>(3 * hidden) * 2,
+                               32 * (i + 1), 64);
+    if (rc) return rc;
+  }
+  return B2_OK;
 }
 
-int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* out,
+int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16* out,
                    const int32_t* lens, int B, int S, int hidden, const int32_t* cu) {
   if (B <= 0 || S <= 0 || (S % QB) != 0 || hidden <= 0 || (hidden % HD) != 0) {
     set_last_error("attention_bf16: needs S %% 128 == 0 and hidden %% 64 == 0 (got S=%d hidden=%d)", S,
@@ -220,8 +272,10 @@ int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* 
   int dev = 0;
   B2_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 64 && !configured[dev]) {
-    B2_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    ATT_SMEM));
+    B2_CUDA_OK(cudaFuncSetAttribute(attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    ATT_SMEM_SINGLE));
+    B2_CUDA_OK(cudaFuncSetAttribute(attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    ATT_SMEM_MULTI));
     configured[dev] = true;
   }
   const int heads = hidden / HD, qblocks = S / QB;
@@ -230,8 +284,13 @@ int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* 
     set_last_error("attention_bf16: grid too large");
     return B2_ERR_ARG;
   }
-  attention_kernel<<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM, stream>>>(
-      tqkv, out, lens, S, hidden, heads, qblocks, cu);
+  const AttMaps& maps = reinterpret_cast<const AttMaps&>(tqkv);
+  if (S == QB)
+    attention_kernel<true><<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM_SINGLE, stream>>>(
+        maps, out, lens, S, hidden, heads, qblocks, cu);
+  else
+    attention_kernel<false><<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM_MULTI, stream>>>(
+        maps, out, lens, S, hidden, heads, qblocks, cu);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }

@@ -24,8 +24,13 @@ int gemm_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& 
 // qkv: [rows, 3*H] bf16 (Q | K | V per token row, head h at columns h*64), out: [rows, H] bf16.
 // lens[b] = number of valid (unpadded) tokens of sequence b; keys >= lens[b] are masked out and
 // query rows >= lens[b] are not written. Sequence b starts at row cu[b] (packed) or b*S (cu null).
-int attention_tmap_qkv(CUtensorMap* out, const void* qkv, int rows, int hidden);
-int attention_bf16(cudaStream_t stream, const CUtensorMap& tqkv, __nv_bfloat16* out,
+// Four tensor maps over the same buffer (TMA boxes of 32, 64, 96 and 128 token rows): the kernel
+// picks the smallest box that covers a sequence's valid rows.
+struct AttentionMaps {
+  alignas(64) unsigned char raw[4 * sizeof(CUtensorMap)];
+};
+int attention_tmaps(AttentionMaps* out, const void* qkv, int rows, int hidden);
+int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16* out,
                    const int32_t* lens, int B, int S, int hidden, const int32_t* cu = nullptr);
 
 // ---- element-wise / row kernels (b2_rows.cu) ---------------------------------------------------
