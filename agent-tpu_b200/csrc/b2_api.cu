@@ -83,7 +83,8 @@ std::vector<TensorSpec> tensor_list(const ModelHeader& m) {
 struct LayerWeights {
   __nv_bfloat16 *Wqkv, *Wo, *W1, *W2;
   float *bqkv, *bo, *b1, *b2, *ln1_g, *ln1_b, *ln2_g, *ln2_b;
-  CUtensorMap tm_qkv, tm_o, tm_1, tm_2;
+  CUtensorMap tm_qkv, tm_o, tm_1, tm_2;      // W maps for the one-CTA GEMM (256-row boxes)
+  CUtensorMap tm2_qkv, tm2_o, tm2_1, tm2_2;  // W maps for the CTA-pair GEMM (128-row boxes)
 };
 
 enum Kind {
@@ -129,6 +130,7 @@ struct b2_handle {
   // packed (padding-free) layout: token rows of a batch are stored back to back, sequence b at
   // rows [cu[b], cu[b+1]); cu[B] is the batch's row count, read by the kernels from device memory
   bool packed = true;
+  bool pair_gemm = true;  // CTA-pair GEMM for the encoder projections (B2_GEMM_1CTA=1 turns it off)
   int32_t* cu = nullptr;
   __nv_bfloat16* cls = nullptr;  // [max_batch, H] gathered [CLS] rows
   CUtensorMap tm_cls{};
@@ -296,6 +298,10 @@ int load_model(b2_handle* h, const char* path) {
       if ((rc = gemm_tmap_b(&L.tm_o, L.Wo, H, H))) break;
       if ((rc = gemm_tmap_b(&L.tm_1, L.W1, I, H))) break;
       if ((rc = gemm_tmap_b(&L.tm_2, L.W2, H, I))) break;
+      if ((rc = gemm2_tmap_b(&L.tm2_qkv, L.Wqkv, 3 * H, H))) break;
+      if ((rc = gemm2_tmap_b(&L.tm2_o, L.Wo, H, H))) break;
+      if ((rc = gemm2_tmap_b(&L.tm2_1, L.W1, I, H))) break;
+      if ((rc = gemm2_tmap_b(&L.tm2_2, L.W2, H, I))) break;
     }
     if (rc) break;
     if ((rc = want_bf16(specs[k++], &h->Wp))) break;
@@ -391,24 +397,31 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
   if ((rc = embed_layernorm(st, h->ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, h->x,
                             M, S, H, m.vocab_size, h->packed ? h->lens : nullptr, cu))) return rc;
   ++*launches;
+  // encoder projections: CTA-pair kernel when the batch is large enough to fill 74 pairs
+  const bool pair = h->pair_gemm && M >= 4096;
+  auto gemm = [&](const CUtensorMap& ta, const CUtensorMap& tb1, const CUtensorMap& tb2, __nv_bfloat16* Cc,
+                  const float* bias, const __nv_bfloat16* res, int N, int K, int ldc, int ldr, int epi) {
+    return pair ? gemm2_bf16_tn(st, ta, tb2, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev)
+                : gemm_bf16_tn(st, ta, tb1, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev);
+  };
   for (uint32_t l = 0; l < m.layers; ++l) {
     LayerWeights& L = h->layers[l];
     mark(h, K_GEMM_QKV);
-    if ((rc = gemm_bf16_tn(st, h->tm_x, L.tm_qkv, h->qkv, L.bqkv, nullptr, M, 3 * H, H, 3 * H, 0,
-                           GEMM_EPI_BIAS, h->num_sms, m_dev))) return rc;
+    if ((rc = gemm(h->tm_x, L.tm_qkv, L.tm2_qkv, h->qkv, L.bqkv, nullptr, 3 * H, H, 3 * H, 0, GEMM_EPI_BIAS)))
+      return rc;
     mark(h, K_ATTENTION);
     if ((rc = attention_bf16(st, h->tm_att, h->ctx, h->lens, B, S, H, cu))) return rc;
     mark(h, K_GEMM_OUT);
-    if ((rc = gemm_bf16_tn(st, h->tm_ctx, L.tm_o, h->y, L.bo, h->x, M, H, H, H, H,
-                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms, m_dev))) return rc;
+    if ((rc = gemm(h->tm_ctx, L.tm_o, L.tm2_o, h->y, L.bo, h->x, H, H, H, H, GEMM_EPI_BIAS_RESIDUAL)))
+      return rc;
     mark(h, K_LAYERNORM);
     if ((rc = layernorm_inplace(st, h->y, L.ln1_g, L.ln1_b, m.ln_eps, M, H, m_dev))) return rc;
     mark(h, K_GEMM_FFN1);
-    if ((rc = gemm_bf16_tn(st, h->tm_y, L.tm_1, h->ffn, L.b1, nullptr, M, I, H, I, 0,
-                           GEMM_EPI_BIAS_GELU, h->num_sms, m_dev))) return rc;
+    if ((rc = gemm(h->tm_y, L.tm_1, L.tm2_1, h->ffn, L.b1, nullptr, I, H, I, 0, GEMM_EPI_BIAS_GELU)))
+      return rc;
     mark(h, K_GEMM_FFN2);
-    if ((rc = gemm_bf16_tn(st, h->tm_ffn, L.tm_2, h->x, L.b2, h->y, M, H, I, H, H,
-                           GEMM_EPI_BIAS_RESIDUAL, h->num_sms, m_dev))) return rc;
+    if ((rc = gemm(h->tm_ffn, L.tm_2, L.tm2_2, h->x, L.b2, h->y, H, I, H, H, GEMM_EPI_BIAS_RESIDUAL)))
+      return rc;
     mark(h, K_LAYERNORM);
     if ((rc = layernorm_inplace(st, h->x, L.ln2_g, L.ln2_b, m.ln_eps, M, H, m_dev))) return rc;
     *launches += 7;
@@ -629,6 +642,8 @@ int b2_create(const b2_config* cfg, b2_handle** out) {
   // against); the default stores only real tokens
   const char* padded_env = getenv("B2_FORCE_PADDED");
   h->packed = !(padded_env && padded_env[0] == '1');
+  const char* one_cta_env = getenv("B2_GEMM_1CTA");
+  h->pair_gemm = !(one_cta_env && one_cta_env[0] == '1');
   if (h->max_batch > 4096) {
     set_last_error("b2_create: max_batch %d exceeds 4096", h->max_batch);
     delete h;

@@ -73,11 +73,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 }
 // Bounded wait: a pipeline bug must surface as a trapped launch (cudaErrorLaunchFailure on the
 // host), never as a hung GPU. try_wait itself sleeps in hardware for a bounded time per probe,
-// so the bound below is tens of seconds of wall clock, far beyond any legitimate wait.
+// so the bound below is between ~50 ms and a few seconds of wall clock, far beyond any legitimate wait.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();
+    if (++spins > (1u << 22)) __trap();
   }
 }
 

@@ -1,0 +1,340 @@
+// b2_gemm2.cu — the encoder GEMM on CTA pairs: tcgen05.mma.cta_group::2, 256 x 256 pair tile.
+//
+//   C[M,N] (bf16) = epilogue( A[M,K] · W[N,K]^T + bias[N] )      (same contract as b2_gemm.cu)
+//
+// Why a second kernel: with one CTA per 128 x 256 tile every SM pulls (128 + 256) x 64 bf16 = 48 KiB
+// from L2 per 512 tensor-pipe cycles (96 B/clk/SM, 14 KB/clk for the chip) and the 4-stage ring only
+// covers ~2,000 cycles of latency; ncu showed the tensor pipe 51% active with L2 and L1 both ~63%
+// busy (profiles/r01_ncu_gemm.md). A CTA pair shares the operands of a 256 x 256 tile: each CTA
+// loads its 128 rows of A and its 128 rows of W (32 KiB per K step, 64 B/clk/SM), the tensor cores
+// of both SMs read both halves of W, and six 32 KiB stages fit where four 48 KiB ones did.
+//
+// Layout of the work
+//   cluster (2,1,1); pair p = blockIdx.x / 2 walks tiles p, p + P, ... (P pairs = SMs / 2)
+//   CTA rank r owns rows [m0 + 128 r, +128) of the tile: loads them (A) and W rows [n0 + 128 r, +128)
+//   warp 0   TMA producer (both CTAs; bytes are counted on the LEADER's full barrier)
+//   warp 1   MMA issuer (leader only): UMMA 256 x 256 x 16, accumulator rows 0-127 in the leader's
+//            TMEM, 128-255 in the peer's; tcgen05.commit multicasts to both CTAs' barriers
+//   warp 2   TMEM allocator (cta_group::2 alloc / dealloc, both CTAs)
+//   warps 4-19 epilogue, each CTA drains its own 128 x 256 accumulator half; accumulator stages are
+//            released on the leader's tmem-empty barrier (the peer arrives remotely)
+#include "b2_kernels.h"
+
+namespace b2 {
+
+namespace {
+
+constexpr int BM = 128;   // rows per CTA (pair tile: 256)
+constexpr int BN = 256;   // columns of the pair tile
+constexpr int BNH = 128;  // W rows each CTA loads
+constexpr int BK = 64;
+constexpr int STAGES = 6;
+constexpr int THREADS = 640;
+constexpr int EPI_WARPS = 16;
+constexpr uint32_t A_BYTES = BM * BK * 2;   // 16 KiB
+constexpr uint32_t B_BYTES = BNH * BK * 2;  // 16 KiB
+constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr uint32_t BAR_BYTES = 8 * (2 * STAGES + 4) + 16;
+constexpr uint32_t SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + BAR_BYTES;
+constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;  // shared::cluster address -> same offset in the even CTA
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this smem offset in every CTA of `mask` once the MMAs issued so far are done
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"(mask)
+      : "memory");
+}
+// TMA load whose completion bytes are counted on the leader CTA's barrier
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst_smem, const CUtensorMap* tmap, uint32_t bar,
+                                                int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar & PEER_MASK), "r"(c0), "r"(c1)
+      : "memory");
+}
+// arrive on the barrier at the same smem offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t"
+      "}"
+      ::"r"(bar), "r"(rank)
+      : "memory");
+}
+
+template <int EPI>
+__device__ __forceinline__ float epi_act(float v) {
+  if (EPI == GEMM_EPI_BIAS_GELU) return gelu_erf(v);
+  if (EPI == GEMM_EPI_BIAS_TANH) return tanhf(v);
+  return v;
+}
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                     const __grid_constant__ CUtensorMap tmap_b, __nv_bfloat16* __restrict__ C,
+                     const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
+                     int M, int N, int K, int ldc, int ldr, const int32_t* __restrict__ m_dev) {
+  extern __shared__ uint8_t smem_raw[];
+  if (m_dev) M = min(M, __ldg(m_dev));
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t sA = base;
+  const uint32_t sB = base + STAGES * A_BYTES;
+  const uint32_t bars = base + STAGES * STAGE_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  const int m_tiles = (M + 2 * BM - 1) / (2 * BM);
+  const int n_tiles = (N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  const int num_kb = (K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 2);   // leader's arrive.expect_tx + the peer producer's remote arrive
+      mbar_init(empty_bar(s), 1);  // one multicast tcgen05.commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 2 * EPI_WARPS);  // epilogue warps of both CTAs (leader's copy is used)
+    }
+    fence_barrier_init();
+  }
+  cluster_sync_all();  // both CTAs' barriers exist before anything arrives on them remotely
+  if (warp == 2) tmem_alloc_2sm(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===== TMA producer (one thread in each CTA) =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs) {
+        const int m_blk = t / n_tiles, n_blk = t % n_tiles;
+        const int arow = m_blk * 2 * BM + rank * BM;
+        const int brow = n_blk * BN + rank * BNH;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (leader) mbar_expect_tx(full_bar(stage), 2 * STAGE_BYTES);
+          else mbar_arrive_cluster(full_bar(stage), 0);
+          tma_load_2d_2sm(sA + stage * A_BYTES, &tmap_a, full_bar(stage), kb * BK, arow);
+          tma_load_2d_2sm(sB + stage * B_BYTES, &tmap_b, full_bar(stage), kb * BK, brow);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one thread of the leader CTA drives both SMs' tensor cores =====
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * BM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint64_t a_desc = umma_desc_sw128(sA + stage * A_BYTES, 16, 1024);
+          const uint64_t b_desc = umma_desc_sw128(sB + stage * B_BYTES, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16_2sm(d_tmem, a_desc + 2u * k, b_desc + 2u * k, idesc, (kb | k) != 0);
+          umma_commit_2sm(empty_bar(stage), 0b11);  // both CTAs' smem slots are free again
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit_2sm(tfull_bar(as), 0b11);  // both accumulator halves complete
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: each CTA drains its own 128 x 256 half =====
+    const int q = warp & 3;
+    const int quarter = (warp - 4) >> 2;
+    int it = 0;
+    for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+      const int m_blk = t / n_tiles, n_blk = t % n_tiles;
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      const int row = m_blk * 2 * BM + rank * BM + q * 32 + lane;
+      const bool row_ok = row < M;
+      const int colq = n_blk * BN + quarter * 64;
+      __nv_bfloat16* crow = C + static_cast<size_t>(row) * ldc;
+      uint4 res[8];
+      if (EPI == GEMM_EPI_BIAS_RESIDUAL) {
+        const __nv_bfloat16* rrow = residual + static_cast<size_t>(row) * ldr;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int col = colq + j * 8;
+          res[j] = (row_ok && col < N) ? __ldg(reinterpret_cast<const uint4*>(rrow + col))
+                                       : make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + quarter * 64;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tbase + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int col = colq + c * 32 + j * 8;
+          if (row_ok && col < N) {
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + col));
+            const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + col + 4));
+            float v[8];
+            v[0] = __uint_as_float(r[j * 8 + 0]) + b0.x;
+            v[1] = __uint_as_float(r[j * 8 + 1]) + b0.y;
+            v[2] = __uint_as_float(r[j * 8 + 2]) + b0.z;
+            v[3] = __uint_as_float(r[j * 8 + 3]) + b0.w;
+            v[4] = __uint_as_float(r[j * 8 + 4]) + b1.x;
+            v[5] = __uint_as_float(r[j * 8 + 5]) + b1.y;
+            v[6] = __uint_as_float(r[j * 8 + 6]) + b1.z;
+            v[7] = __uint_as_float(r[j * 8 + 7]) + b1.w;
+            if (EPI == GEMM_EPI_BIAS_RESIDUAL) {
+              const uint4 rv = res[c * 4 + j];
+              v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x);
+              v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
+              v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z);
+              v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = epi_act<EPI>(v[e]);
+            uint4 o;
+            o.x = pack_bf16x2(v[0], v[1]);
+            o.y = pack_bf16x2(v[2], v[3]);
+            o.z = pack_bf16x2(v[4], v[5]);
+            o.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4*>(crow + col) = o;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);  // the issuer waits on the leader's copy
+    }
+  }
+
+  __syncwarp();  // reconverge the single-thread roles before the aligned cluster barrier
+  tc_fence_before();
+  cluster_sync_all();  // neither CTA may free TMEM (or exit) while the other still uses the pair
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, 512);
+  }
+}
+
+template <int EPI>
+int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, __nv_bfloat16* C,
+            const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int ldc, int ldr,
+            int num_sms, const int32_t* m_dev) {
+  static bool configured[64] = {};
+  int dev = 0;
+  B2_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 64 && !configured[dev]) {
+    B2_CUDA_OK(cudaFuncSetAttribute(gemm2_bf16_tn_kernel<EPI>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    configured[dev] = true;
+  }
+  const int tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN);
+  int pairs = num_sms / 2;
+  if (tiles < pairs) pairs = tiles;
+  gemm2_bf16_tn_kernel<EPI><<<2 * pairs, THREADS, SMEM_BYTES, stream>>>(ta, tb, C, bias, residual, M, N,
+                                                                       K, ldc, ldr, m_dev);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+}  // namespace
+
+// W tensor map for the pair kernel: each CTA loads 128 rows of W per K step.
+int gemm2_tmap_b(CUtensorMap* out, const void* W, int N, int K) {
+  return make_tmap_bf16_2d(out, W, N, K, static_cast<uint64_t>(K) * 2, BNH, BK);
+}
+
+int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb,
+                  __nv_bfloat16* C, const float* bias, const __nv_bfloat16* residual, int M, int N,
+                  int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev) {
+  if (M <= 0 || N <= 0 || K <= 0 || (N % 8) != 0 || (K % 8) != 0 || (ldc % 8) != 0 || num_sms < 2) {
+    set_last_error("gemm2_bf16_tn: bad shape M=%d N=%d K=%d ldc=%d (N, K, ldc must be multiples of 8)",
+                   M, N, K, ldc);
+    return B2_ERR_ARG;
+  }
+  switch (epilogue) {
+    case GEMM_EPI_BIAS:
+      return launch2<GEMM_EPI_BIAS>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms, m_dev);
+    case GEMM_EPI_BIAS_GELU:
+      return launch2<GEMM_EPI_BIAS_GELU>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms,
+                                         m_dev);
+    case GEMM_EPI_BIAS_RESIDUAL:
+      if (!residual || (ldr % 8) != 0) {
+        set_last_error("gemm2_bf16_tn: residual epilogue needs a residual pointer and ldr %% 8 == 0");
+        return B2_ERR_ARG;
+      }
+      return launch2<GEMM_EPI_BIAS_RESIDUAL>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr,
+                                             num_sms, m_dev);
+    case GEMM_EPI_BIAS_TANH:
+      return launch2<GEMM_EPI_BIAS_TANH>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms,
+                                         m_dev);
+  }
+  set_last_error("gemm2_bf16_tn: unknown epilogue %d", epilogue);
+  return B2_ERR_ARG;
+}
+
+}  // namespace b2

@@ -37,7 +37,7 @@ static float bf16_round(float f) { return __bfloat162float(__float2bfloat16(f));
 
 static double gelu_ref(double x) { return 0.5 * x * (1.0 + erf(x / sqrt(2.0))); }
 
-static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it) {
+static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it, bool pair = false) {
   std::vector<__nv_bfloat16> hA((size_t)M * K), hW((size_t)N * K), hR((size_t)M * N);
   std::vector<float> fA((size_t)M * K), fW((size_t)N * K), fR((size_t)M * N), hb(N);
   for (size_t i = 0; i < hA.size(); ++i) { fA[i] = bf16_round(frand()); hA[i] = __float2bfloat16(fA[i]); }
@@ -58,8 +58,10 @@ static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it) {
   CK(cudaMemset(dC, 0xFF, (size_t)M * N * 2));
   CUtensorMap ta, tb;
   B2(gemm_tmap_a(&ta, dA, M, K, K));
-  B2(gemm_tmap_b(&tb, dW, N, K));
-  B2(gemm_bf16_tn(0, ta, tb, dC, db, dR, M, N, K, N, N, epi, num_sms));
+  if (pair) B2(gemm2_tmap_b(&tb, dW, N, K)); else B2(gemm_tmap_b(&tb, dW, N, K));
+  auto run = [&]() { return pair ? gemm2_bf16_tn(0, ta, tb, dC, db, dR, M, N, K, N, N, epi, num_sms)
+                                 : gemm_bf16_tn(0, ta, tb, dC, db, dR, M, N, K, N, N, epi, num_sms); };
+  B2(run());
   CK(cudaDeviceSynchronize());
   std::vector<__nv_bfloat16> hC((size_t)M * N);
   CK(cudaMemcpy(hC.data(), dC, hC.size() * 2, cudaMemcpyDeviceToHost));
@@ -83,16 +85,16 @@ static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it) {
     if (err > max_err) max_err = err;
     ++checked;
   }
-  printf("gemm M=%d N=%d K=%d epi=%d: checked=%zu bad=%zu max_abs_err=%.5f %s\n", M, N, K, epi,
+  printf("gemm%s M=%d N=%d K=%d epi=%d: checked=%zu bad=%zu max_abs_err=%.5f %s\n", pair ? "2" : "", M, N, K, epi,
          checked, bad, max_err, bad ? "FAIL" : "ok");
   if (time_it && !bad) {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    for (int i = 0; i < 3; ++i) B2(gemm_bf16_tn(0, ta, tb, dC, db, dR, M, N, K, N, N, epi, num_sms));
+    for (int i = 0; i < 3; ++i) B2(run());
     CK(cudaEventRecord(e0));
     const int iters = 10;
-    for (int i = 0; i < iters; ++i) B2(gemm_bf16_tn(0, ta, tb, dC, db, dR, M, N, K, N, N, epi, num_sms));
+    for (int i = 0; i < iters; ++i) B2(run());
     CK(cudaEventRecord(e1));
     CK(cudaEventSynchronize(e1));
     float ms;
@@ -301,6 +303,23 @@ int main(int argc, char** argv) {
     fails += check_gemm(1024, 3072, 768, GEMM_EPI_BIAS_GELU, sms, false);
     fails += check_gemm(512, 768, 768, GEMM_EPI_BIAS_TANH, sms, false);
     fails += check_gemm(40000, 2304, 768, GEMM_EPI_BIAS, sms, false);   // > 148 tiles: persistence
+  }
+  if (!strcmp(what, "all") || !strcmp(what, "gemm2")) {
+    fails += check_gemm(256, 256, 64, GEMM_EPI_BIAS, sms, false, true);
+    fails += check_gemm(256, 256, 768, GEMM_EPI_BIAS, sms, false, true);
+    fails += check_gemm(512, 512, 128, GEMM_EPI_BIAS, sms, false, true);
+    fails += check_gemm(200, 264, 72, GEMM_EPI_BIAS, sms, false, true);
+    fails += check_gemm(1000, 768, 3072, GEMM_EPI_BIAS_RESIDUAL, sms, false, true);
+    fails += check_gemm(1024, 3072, 768, GEMM_EPI_BIAS_GELU, sms, false, true);
+    fails += check_gemm(40000, 2304, 768, GEMM_EPI_BIAS, sms, false, true);
+  }
+  if (!strcmp(what, "all") || !strcmp(what, "gemm2perf")) {
+    fails += check_gemm(131072, 2304, 768, GEMM_EPI_BIAS, sms, true, true);
+    fails += check_gemm(131072, 768, 768, GEMM_EPI_BIAS_RESIDUAL, sms, true, true);
+    fails += check_gemm(131072, 3072, 768, GEMM_EPI_BIAS_GELU, sms, true, true);
+    fails += check_gemm(131072, 768, 3072, GEMM_EPI_BIAS_RESIDUAL, sms, true, true);
+    fails += check_gemm(71000, 2304, 768, GEMM_EPI_BIAS, sms, true, true);
+    fails += check_gemm(71000, 768, 768, GEMM_EPI_BIAS_RESIDUAL, sms, true, true);
   }
   if (!strcmp(what, "all") || !strcmp(what, "gemmperf")) {
     fails += check_gemm(131072, 2304, 768, GEMM_EPI_BIAS, sms, true);
