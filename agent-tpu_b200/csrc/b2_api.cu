@@ -132,8 +132,10 @@ struct b2_handle {
   bool packed = true;
   bool pair_gemm = true;  // CTA-pair GEMM for the encoder projections (B2_GEMM_1CTA=1 turns it off)
   int32_t* cu = nullptr;
-  __nv_bfloat16* cls = nullptr;  // [max_batch, H] gathered [CLS] rows
-  CUtensorMap tm_cls{};
+  // [CLS]-only tail of the last layer: after its attention only row 0 of every sequence feeds the
+  // pooler, so the out-projection, FFN and both LayerNorms of that layer run on [B, *] blocks
+  __nv_bfloat16 *cls = nullptr, *cls_ctx = nullptr, *cls_y = nullptr, *cls_f = nullptr;
+  CUtensorMap tm_cls{}, tm_cls_ctx{}, tm_cls_y{}, tm_cls_f{};
 
   // growable staging for host-pointer calls
   uint8_t* st_text = nullptr; size_t st_text_cap = 0;
@@ -344,6 +346,15 @@ int alloc_activations(b2_handle* h) {
   if ((rc = A(reinterpret_cast<void**>(&h->cls), int64_t(h->max_batch) * H * 2))) return rc;
   B2_CUDA_OK(cudaMemsetAsync(h->cls, 0, int64_t(h->max_batch) * H * 2, h->stream));
   if ((rc = gemm_tmap_a(&h->tm_cls, h->cls, h->max_batch, H, H))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->cls_ctx), int64_t(h->max_batch) * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->cls_y), int64_t(h->max_batch) * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->cls_f), int64_t(h->max_batch) * I * 2))) return rc;
+  B2_CUDA_OK(cudaMemsetAsync(h->cls_ctx, 0, int64_t(h->max_batch) * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->cls_y, 0, int64_t(h->max_batch) * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->cls_f, 0, int64_t(h->max_batch) * I * 2, h->stream));
+  if ((rc = gemm_tmap_a(&h->tm_cls_ctx, h->cls_ctx, h->max_batch, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&h->tm_cls_y, h->cls_y, h->max_batch, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&h->tm_cls_f, h->cls_f, h->max_batch, I, I))) return rc;
   // pad rows are read by TMA boxes and attention tiles before they are ever written: give them
   // finite contents once so no NaN bit pattern can reach a masked-out product
   B2_CUDA_OK(cudaMemsetAsync(h->x, 0, rows * H * 2, h->stream));
@@ -411,6 +422,27 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
       return rc;
     mark(h, K_ATTENTION);
     if ((rc = attention_bf16(st, h->tm_att, h->ctx, h->lens, B, S, H, cu))) return rc;
+    if (l + 1 == m.layers) {
+      // last layer: only the [CLS] rows are read downstream (pooler), and every remaining kernel is
+      // row-wise, so run them on the B gathered rows; per-row results are unchanged
+      mark(h, K_GEMM_OUT);
+      if ((rc = gather_cls_rows(st, h->ctx, cu, S, B, H, h->cls_ctx))) return rc;
+      if ((rc = gather_cls_rows(st, h->x, cu, S, B, H, h->cls))) return rc;
+      if ((rc = gemm_bf16_tn(st, h->tm_cls_ctx, L.tm_o, h->cls_y, L.bo, h->cls, B, H, H, H, H,
+                             GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
+      mark(h, K_LAYERNORM);
+      if ((rc = layernorm_inplace(st, h->cls_y, L.ln1_g, L.ln1_b, m.ln_eps, B, H))) return rc;
+      mark(h, K_GEMM_FFN1);
+      if ((rc = gemm_bf16_tn(st, h->tm_cls_y, L.tm_1, h->cls_f, L.b1, nullptr, B, I, H, I, 0,
+                             GEMM_EPI_BIAS_GELU, h->num_sms))) return rc;
+      mark(h, K_GEMM_FFN2);
+      if ((rc = gemm_bf16_tn(st, h->tm_cls_f, L.tm_2, h->cls, L.b2, h->cls_y, B, H, I, H, H,
+                             GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
+      mark(h, K_LAYERNORM);
+      if ((rc = layernorm_inplace(st, h->cls, L.ln2_g, L.ln2_b, m.ln_eps, B, H))) return rc;
+      *launches += 9;
+      break;
+    }
     mark(h, K_GEMM_OUT);
     if ((rc = gemm(h->tm_ctx, L.tm_o, L.tm2_o, h->y, L.bo, h->x, H, H, H, H, GEMM_EPI_BIAS_RESIDUAL)))
       return rc;
@@ -427,19 +459,8 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
     *launches += 7;
   }
   mark(h, K_POOLER);
-  if (h->packed) {
-    // pooler over the [CLS] rows: row cu[b] of every sequence, gathered into a dense [B, H] block
-    if ((rc = gather_cls_rows(st, h->x, h->cu, B, H, h->cls))) return rc;
-    ++*launches;
-    if ((rc = gemm_bf16_tn(st, h->tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
-                           GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
-  } else {
-    // padded layout: the [CLS] rows are a strided view of x (row pitch S*H) through the A tensor map
-    CUtensorMap tm_cls;
-    if ((rc = gemm_tmap_a(&tm_cls, h->x, B, H, int64_t(S) * H))) return rc;
-    if ((rc = gemm_bf16_tn(st, tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
-                           GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
-  }
+  if ((rc = gemm_bf16_tn(st, h->tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
+                         GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
   mark(h, K_HEAD);
   if ((rc = classify_head(st, h->pooled, H, h->Wc, h->bc, B, H, m.num_labels, topk, d_logits,
                           d_top_idx, d_top_score, d_labels, h->hist))) return rc;

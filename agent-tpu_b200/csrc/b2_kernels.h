@@ -52,9 +52,9 @@ int layernorm_inplace(cudaStream_t stream, __nv_bfloat16* x, const float* gamma,
                       float eps, int rows, int hidden, const int32_t* rows_dev = nullptr);
 // cu[0..B] = exclusive prefix sum of lens, cu[B] = total rows (also the GEMMs' m_dev); B <= 4096.
 int pack_offsets(cudaStream_t stream, const int32_t* lens, int B, int32_t* cu);
-// dst[b, :] = src[cu[b], :]   (the [CLS] row of every packed sequence)
-int gather_cls_rows(cudaStream_t stream, const __nv_bfloat16* src, const int32_t* cu, int B, int hidden,
-                    __nv_bfloat16* dst);
+// dst[b, :] = src[first row of sequence b, :]  (the [CLS] rows): row cu[b] (packed) or b*S (cu null)
+int gather_cls_rows(cudaStream_t stream, const __nv_bfloat16* src, const int32_t* cu, int S, int B,
+                    int hidden, __nv_bfloat16* dst);
 // logits[b, c] = pooled[b,:] · Wc[c,:] + bc[c]; probs = softmax(logits); top-k (descending, ties
 // by lower index), label = argmax, histogram[label] += 1.
 int classify_head(cudaStream_t stream, const __nv_bfloat16* pooled, int ld_pooled, const float* Wc,

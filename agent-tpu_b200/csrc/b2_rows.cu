@@ -231,10 +231,11 @@ __global__ void __launch_bounds__(1024) pack_offsets_kernel(const int32_t* __res
 }
 
 __global__ void gather_cls_kernel(const __nv_bfloat16* __restrict__ src, const int32_t* __restrict__ cu,
-                                  int B, int hidden, __nv_bfloat16* __restrict__ dst) {
+                                  int S, int B, int hidden, __nv_bfloat16* __restrict__ dst) {
   const int b = blockIdx.x;
   if (b >= B) return;
-  const uint2* s = reinterpret_cast<const uint2*>(src + static_cast<size_t>(cu[b]) * hidden);
+  const size_t row = cu ? static_cast<size_t>(cu[b]) : static_cast<size_t>(b) * S;
+  const uint2* s = reinterpret_cast<const uint2*>(src + row * hidden);
   uint2* d = reinterpret_cast<uint2*>(dst + static_cast<size_t>(b) * hidden);
   for (int i = threadIdx.x; i < hidden / 4; i += blockDim.x) d[i] = s[i];
 }
@@ -310,10 +311,10 @@ int pack_offsets(cudaStream_t stream, const int32_t* lens, int B, int32_t* cu) {
   return B2_OK;
 }
 
-int gather_cls_rows(cudaStream_t stream, const __nv_bfloat16* src, const int32_t* cu, int B, int hidden,
-                    __nv_bfloat16* dst) {
+int gather_cls_rows(cudaStream_t stream, const __nv_bfloat16* src, const int32_t* cu, int S, int B,
+                    int hidden, __nv_bfloat16* dst) {
   if (B <= 0) return B2_OK;
-  gather_cls_kernel<<<B, 128, 0, stream>>>(src, cu, B, hidden, dst);
+  gather_cls_kernel<<<B, 128, 0, stream>>>(src, cu, S, B, hidden, dst);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }

@@ -349,9 +349,11 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     packed_rows = bool(eng.info.packed_rows)
     if packed_rows:
         rows = tokens       # padding-free layout: the kernels process real token rows only
-    flop = {"gemm_qkv": 2.0 * rows * 3 * H * H * L, "gemm_attn_out": 2.0 * rows * H * H * L,
-            "gemm_ffn1": 2.0 * rows * I * H * L, "gemm_ffn2": 2.0 * rows * H * I * L}
-    byts = {"attention": 4.0 * rows * H * 2 * L, "layernorm": 2.0 * rows * H * 2 * 2 * L,
+    # the last layer's out-projection / FFN run on the [CLS] rows only (one row per item)
+    tail_rows = rows * (L - 1) + float(n * args.steps)
+    flop = {"gemm_qkv": 2.0 * rows * 3 * H * H * L, "gemm_attn_out": 2.0 * tail_rows * H * H,
+            "gemm_ffn1": 2.0 * tail_rows * I * H, "gemm_ffn2": 2.0 * tail_rows * H * I}
+    byts = {"attention": 4.0 * rows * H * 2 * L, "layernorm": 2.0 * tail_rows * H * 2 * 2,
             "embed": rows * (H * 4 + H * 2 + 4.0),
             "tokenize": float(sum(int(o[-1]) + 8 * (len(o) - 1) for _, o in packed[args.warmup:]) + 5 * S * n * args.steps)}
     kernels = []
