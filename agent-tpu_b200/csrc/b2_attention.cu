@@ -20,6 +20,8 @@
 // No reference counterpart: the reference's model is an opaque TFLite graph
 // (ops/map_classify_tpu.py:71-72). Semantics follow BertSelfAttention (scores/sqrt(d) + additive
 // key mask, softmax in f32, context = probs·V).
+#include <cstdlib>
+
 #include "b2_kernels.h"
 
 namespace b2 {
@@ -247,6 +249,205 @@ attention_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict
   }
 }
 
+// ---- persistent, software-pipelined variant for S = 128 (one key block per sequence) -------------
+// Two CTAs per SM, each walking (sequence, head) items i = blockIdx.x, + gridDim.x, ... with two
+// stages of {Q, K, V} tiles in shared memory and two S/O accumulators in TMEM:
+//   control thread : loads for item i+2 are in flight while item i+1's Q·Kᵀ is issued right behind
+//                    item i's P·V, so the tensor core never waits for a load and the softmax warps
+//                    never wait for Q·Kᵀ;
+//   softmax warps  : S_i (TMEM) -> P_i (smem, over the dead Q|K tiles of the same stage) ->
+//                    O_i (TMEM, over S_i) -> scaled bf16 rows to global.
+// Per-item set-up (TMEM allocation, barrier initialisation, CTA launch) is paid once per CTA
+// instead of 12,288 times per layer.
+constexpr uint32_t STAGE_BYTES_P = 3 * TILE_BYTES;
+constexpr uint32_t ATT_SMEM_PERSIST = 1024 + 2 * STAGE_BYTES_P + 128;
+
+__global__ void __launch_bounds__(ATT_THREADS, 2)
+attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
+                         const int32_t* __restrict__ lens, int S, int hidden, int heads, int n_items,
+                         const int32_t* __restrict__ cu) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bars = base + 2 * STAGE_BYTES_P;
+  // per stage s: qkv_full, s_full, p_full, o_full, free
+  auto bar = [&](int which, int s) { return bars + 8u * (which * 2 + s); };
+  enum { QKV_FULL = 0, S_FULL = 1, P_FULL = 2, O_FULL = 3, FREE = 4 };
+  const uint32_t tmem_slot = bars + 8u * 10;
+  uint8_t* smem_aligned = smem_raw + (base - raw);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int my_items = (n_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                       static_cast<int>(gridDim.x);
+
+  if (threadIdx.x == 128) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar(QKV_FULL, s), 1);
+      mbar_init(bar(S_FULL, s), 1);
+      mbar_init(bar(P_FULL, s), 128);
+      mbar_init(bar(O_FULL, s), 1);
+      mbar_init(bar(FREE, s), 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 4) tmem_alloc<256>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      auto load_item = [&](int i) {
+        const int idx = blockIdx.x + i * gridDim.x;
+        const int b = idx / heads, h = idx - b * heads;
+        int len = lens[b];
+        len = len < 1 ? 1 : (len > S ? S : len);
+        const int row0 = cu ? cu[b] : b * S;
+        const int box = (len + 31) >> 5;
+        const int s = i & 1;
+        const uint32_t st = base + s * STAGE_BYTES_P;
+        mbar_expect_tx(bar(QKV_FULL, s), 3 * box * 32 * 128);
+        tma_load_2d(st, &maps.m[box - 1], bar(QKV_FULL, s), h * HD, row0);
+        tma_load_2d(st + TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), hidden + h * HD, row0);
+        tma_load_2d(st + 2 * TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), 2 * hidden + h * HD, row0);
+      };
+      auto nk_of = [&](int i) {
+        const int idx = blockIdx.x + i * gridDim.x;
+        int len = lens[idx / heads];
+        len = len < 1 ? 1 : (len > S ? S : len);
+        return ((len + 31) >> 5) * 32;
+      };
+      auto issue_s = [&](int i) {
+        const int s = i & 1;
+        const uint32_t st = base + s * STAGE_BYTES_P;
+        mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
+        tc_fence_after();
+        const uint32_t idesc_s = umma_idesc_bf16(128, nk_of(i), 0, 0);
+        const uint64_t qd = umma_desc_sw128(st, 16, 1024);
+        const uint64_t kd = umma_desc_sw128(st + TILE_BYTES, 16, 1024);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16(tmem_base + s * 128, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
+        umma_commit(bar(S_FULL, s));
+      };
+      if (my_items > 0) load_item(0);
+      if (my_items > 1) load_item(1);
+      if (my_items > 0) issue_s(0);
+      for (int i = 0; i < my_items; ++i) {
+        const int s = i & 1;
+        const uint32_t ph = (i >> 1) & 1;
+        const uint32_t st = base + s * STAGE_BYTES_P;
+        const int nk = nk_of(i);
+        mbar_wait(bar(P_FULL, s), ph);
+        tc_fence_after();
+        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
+        for (int k = 0; k < nk / 16; ++k) {
+          const uint64_t pd = umma_desc_sw128(st + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
+          const uint64_t vd = umma_desc_sw128(st + 2 * TILE_BYTES + k * 2048, 8192, 1024);
+          umma_bf16(tmem_base + s * 128, pd, vd, idesc_o, k != 0);
+        }
+        umma_commit(bar(O_FULL, s));
+        if (i + 1 < my_items) issue_s(i + 1);  // right behind P·V: the softmax warps find S ready
+        if (i + 2 < my_items) {
+          mbar_wait(bar(FREE, s), ph);  // O_i has been read: stage s (smem and TMEM) is free again
+          load_item(i + 2);
+        }
+      }
+    }
+  } else {
+    const int r = threadIdx.x;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
+    for (int i = 0; i < my_items; ++i) {
+      const int s = i & 1;
+      const uint32_t ph = (i >> 1) & 1;
+      const int idx = blockIdx.x + i * gridDim.x;
+      const int b = idx / heads, h = idx - b * heads;
+      int len = lens[b];
+      len = len < 1 ? 1 : (len > S ? S : len);
+      const int row0 = cu ? cu[b] : b * S;
+      const uint32_t tS = tmem_base + s * 128 + lane_base;
+      mbar_wait(bar(S_FULL, s), ph);
+      tc_fence_after();
+      float mx = -INFINITY;
+      for (int c = 0; c < 4; ++c) {
+        if (c * 32 < len) {
+          uint32_t v[32];
+          tmem_ld_32x32(tS + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c * 32 + j < len) mx = fmaxf(mx, __uint_as_float(v[j]));
+        }
+      }
+      const float moff = mx * sl2;
+      float rowsum = 0.f;
+      for (int c = 0; c < 4; ++c) {
+        if (c * 32 < len) {
+          uint32_t packed[16];
+          uint32_t v[32];
+          tmem_ld_32x32(tS + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const float p0 = (c * 32 + j < len) ? ex2_approx(fmaf(__uint_as_float(v[j]), sl2, -moff)) : 0.f;
+            const float p1 = (c * 32 + j + 1 < len) ? ex2_approx(fmaf(__uint_as_float(v[j + 1]), sl2, -moff)) : 0.f;
+            rowsum += p0 + p1;
+            packed[j >> 1] = pack_bf16x2(p0, p1);
+          }
+          uint8_t* tile = smem_aligned + s * STAGE_BYTES_P + (c >> 1) * TILE_BYTES + r * 128;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
+            *reinterpret_cast<uint4*>(tile + chunk * 16) =
+                make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
+          }
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar(P_FULL, s));
+
+      const float inv = rowsum > 0.f ? 1.0f / rowsum : 0.f;
+      __nv_bfloat16* dst = out + static_cast<size_t>(row0 + r) * hidden + h * HD;
+      const bool store = r < len;
+      mbar_wait(bar(O_FULL, s), ph);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tS + c * 32, v);
+        tmem_ld_wait();
+        if (store) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 w;
+            w.x = pack_bf16x2(__uint_as_float(v[j * 8 + 0]) * inv, __uint_as_float(v[j * 8 + 1]) * inv);
+            w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
+            w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
+            w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + c * 32 + j * 8) = w;
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(bar(FREE, s));
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem_base);
+  }
+}
+
 }  // namespace
 
 // `out` holds four tensor maps (box rows 32, 64, 96, 128) packed into AttentionMaps::raw.
@@ -276,6 +477,8 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
                                     ATT_SMEM_SINGLE));
     B2_CUDA_OK(cudaFuncSetAttribute(attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     ATT_SMEM_MULTI));
+    B2_CUDA_OK(cudaFuncSetAttribute(attention_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    ATT_SMEM_PERSIST));
     configured[dev] = true;
   }
   const int heads = hidden / HD, qblocks = S / QB;
@@ -285,7 +488,15 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
     return B2_ERR_ARG;
   }
   const AttMaps& maps = reinterpret_cast<const AttMaps&>(tqkv);
-  if (S == QB)
+  static const bool one_shot = [] { const char* e = getenv("B2_ATTN_ONESHOT"); return e && e[0] == '1'; }();
+  if (S == QB && !one_shot) {
+    int sms = 0;
+    B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int items = B * heads;
+    const int ctas = items < 2 * sms ? items : 2 * sms;
+    attention_persist_kernel<<<ctas, ATT_THREADS, ATT_SMEM_PERSIST, stream>>>(maps, out, lens, S, hidden,
+                                                                             heads, items, cu);
+  } else if (S == QB)
     attention_kernel<true><<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM_SINGLE, stream>>>(
         maps, out, lens, S, hidden, heads, qblocks, cu);
   else
