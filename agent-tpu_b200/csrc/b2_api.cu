@@ -85,6 +85,12 @@ struct LayerWeights {
   float *bqkv, *bo, *b1, *b2, *ln1_g, *ln1_b, *ln2_g, *ln2_b;
   CUtensorMap tm_qkv, tm_o, tm_1, tm_2;      // W maps for the one-CTA GEMM (256-row boxes)
   CUtensorMap tm2_qkv, tm2_o, tm2_1, tm2_2;  // W maps for the CTA-pair GEMM (128-row boxes)
+  // LayerNorm folded into the Linear that follows it (GemmLnArgs in b2_kernels.h): the QKV
+  // projection absorbs the previous layer's output LayerNorm, FFN1 absorbs this layer's attention
+  // LayerNorm. W*_f = bf16(gamma ∘ W), g = its row sums, c = bias + W·beta.
+  __nv_bfloat16 *Wqkv_f = nullptr, *W1_f = nullptr;
+  float *g_qkv = nullptr, *c_qkv = nullptr, *g_1 = nullptr, *c_1 = nullptr;
+  CUtensorMap tm2_qkv_f, tm2_1_f;
 };
 
 enum Kind {
@@ -131,6 +137,12 @@ struct b2_handle {
   // rows [cu[b], cu[b+1]); cu[B] is the batch's row count, read by the kernels from device memory
   bool packed = true;
   bool pair_gemm = true;  // CTA-pair GEMM for the encoder projections (B2_GEMM_1CTA=1 turns it off)
+  // LayerNorm folding (B2_NO_LN_FOLD=1 turns it off): no LayerNorm kernel runs in the encoder; the
+  // un-normalised sums stay in x / y and (mean, rstd) per row travel in stats_a / stats_b
+  bool fold_ln = true;
+  float2 *stats_a = nullptr, *stats_b = nullptr, *part = nullptr;
+  float *ones = nullptr, *zeros = nullptr;
+  int part_slots = 0;
   int32_t* cu = nullptr;
   // [CLS]-only tail of the last layer: after its attention only row 0 of every sequence feeds the
   // pooler, so the out-projection, FFN and both LayerNorms of that layer run on [B, *] blocks
@@ -283,14 +295,34 @@ int load_model(b2_handle* h, const char* path) {
     if ((rc = want_f32(specs[k++], &h->emb_b))) break;
     for (uint32_t l = 0; l < m.layers && !rc; ++l) {
       LayerWeights& L = h->layers[l];
-      if ((rc = want_bf16(specs[k++], &L.Wqkv))) break;
+      const int Hh = m.hidden, Ii = m.intermediate;
+      if ((rc = want_bf16(specs[k++], &L.Wqkv))) break;   // f32 copy stays in `scratch` until folded
       if ((rc = want_f32(specs[k++], &L.bqkv))) break;
+      {
+        // the QKV projection reads the previous layer's output LayerNorm (none before layer 0)
+        const float* pg = l ? h->layers[l - 1].ln2_g : nullptr;
+        const float* pb = l ? h->layers[l - 1].ln2_b : nullptr;
+        if ((rc = dev_alloc(h, reinterpret_cast<void**>(&L.Wqkv_f), size_t(3) * Hh * Hh * 2))) break;
+        if ((rc = dev_alloc(h, reinterpret_cast<void**>(&L.g_qkv), size_t(3) * Hh * 4))) break;
+        if ((rc = dev_alloc(h, reinterpret_cast<void**>(&L.c_qkv), size_t(3) * Hh * 4))) break;
+        h->weight_bytes += size_t(3) * Hh * Hh * 2;
+        if ((rc = fold_ln_into_linear(h->stream, scratch, L.bqkv, pg, pb, 3 * Hh, Hh, L.Wqkv_f, L.g_qkv,
+                                      L.c_qkv))) break;
+      }
       if ((rc = want_bf16(specs[k++], &L.Wo))) break;
       if ((rc = want_f32(specs[k++], &L.bo))) break;
       if ((rc = want_f32(specs[k++], &L.ln1_g))) break;
       if ((rc = want_f32(specs[k++], &L.ln1_b))) break;
       if ((rc = want_bf16(specs[k++], &L.W1))) break;
       if ((rc = want_f32(specs[k++], &L.b1))) break;
+      {
+        if ((rc = dev_alloc(h, reinterpret_cast<void**>(&L.W1_f), size_t(Ii) * Hh * 2))) break;
+        if ((rc = dev_alloc(h, reinterpret_cast<void**>(&L.g_1), size_t(Ii) * 4))) break;
+        if ((rc = dev_alloc(h, reinterpret_cast<void**>(&L.c_1), size_t(Ii) * 4))) break;
+        h->weight_bytes += size_t(Ii) * Hh * 2;
+        if ((rc = fold_ln_into_linear(h->stream, scratch, L.b1, L.ln1_g, L.ln1_b, Ii, Hh, L.W1_f, L.g_1,
+                                      L.c_1))) break;
+      }
       if ((rc = want_bf16(specs[k++], &L.W2))) break;
       if ((rc = want_f32(specs[k++], &L.b2))) break;
       if ((rc = want_f32(specs[k++], &L.ln2_g))) break;
@@ -304,6 +336,8 @@ int load_model(b2_handle* h, const char* path) {
       if ((rc = gemm2_tmap_b(&L.tm2_o, L.Wo, H, H))) break;
       if ((rc = gemm2_tmap_b(&L.tm2_1, L.W1, I, H))) break;
       if ((rc = gemm2_tmap_b(&L.tm2_2, L.W2, H, I))) break;
+      if ((rc = gemm2_tmap_b(&L.tm2_qkv_f, L.Wqkv_f, 3 * H, H))) break;
+      if ((rc = gemm2_tmap_b(&L.tm2_1_f, L.W1_f, I, H))) break;
     }
     if (rc) break;
     if ((rc = want_bf16(specs[k++], &h->Wp))) break;
@@ -343,6 +377,15 @@ int alloc_activations(b2_handle* h) {
   if ((rc = A(reinterpret_cast<void**>(&h->pooled), int64_t(h->max_batch) * H * 2))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->hist), int64_t(m.num_labels) * 8))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->cu), (int64_t(h->max_batch) + 1) * 4))) return rc;
+  h->part_slots = static_cast<int>((H + 63) / 64);
+  if ((rc = A(reinterpret_cast<void**>(&h->stats_a), rows * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->stats_b), rows * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->part), rows * h->part_slots * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->ones), H * 4))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->zeros), H * 4))) return rc;
+  B2_CUDA_OK(cudaMemsetAsync(h->zeros, 0, H * 4, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->part, 0, rows * h->part_slots * 8, h->stream));
+  if ((rc = fill_synthetic_f32(h->stream, h->ones, H, 0, 0, 0.0f, 1.0f))) return rc;  // 0*x + 1
   if ((rc = A(reinterpret_cast<void**>(&h->cls), int64_t(h->max_batch) * H * 2))) return rc;
   B2_CUDA_OK(cudaMemsetAsync(h->cls, 0, int64_t(h->max_batch) * H * 2, h->stream));
   if ((rc = gemm_tmap_a(&h->tm_cls, h->cls, h->max_batch, H, H))) return rc;
@@ -415,11 +458,33 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
     return pair ? gemm2_bf16_tn(st, ta, tb2, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev)
                 : gemm_bf16_tn(st, ta, tb1, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev);
   };
+  const bool fold = h->fold_ln;
+  // folded path: x / y hold un-normalised sums; the LayerNorm that turns them into layer inputs is
+  // described by (stats, gamma, beta) and applied inside the consuming GEMMs' epilogues
+  const float2* in_stats = h->stats_b;
+  const float* in_g = h->ones;
+  const float* in_b = h->zeros;
+  if (fold) {
+    if ((rc = ln_stats_identity(st, h->stats_b, M))) return rc;  // the embedding output is normalised
+    ++*launches;
+  }
+  auto gemm_ln = [&](const CUtensorMap& ta, const CUtensorMap& tb, __nv_bfloat16* Cc, const float* bias,
+                     const __nv_bfloat16* res, int N, int K, int ldc, int ldr, int epi, const GemmLnArgs& a) {
+    return gemm2_bf16_tn(st, ta, tb, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev, &a);
+  };
   for (uint32_t l = 0; l < m.layers; ++l) {
     LayerWeights& L = h->layers[l];
     mark(h, K_GEMM_QKV);
-    if ((rc = gemm(h->tm_x, L.tm_qkv, L.tm2_qkv, h->qkv, L.bqkv, nullptr, 3 * H, H, 3 * H, 0, GEMM_EPI_BIAS)))
+    if (fold) {
+      GemmLnArgs a;
+      a.row_stats = in_stats;
+      a.g = L.g_qkv;
+      if ((rc = gemm_ln(h->tm_x, L.tm2_qkv_f, h->qkv, L.c_qkv, nullptr, 3 * H, H, 3 * H, 0, GEMM_EPI_LNIN, a)))
+        return rc;
+    } else if ((rc = gemm(h->tm_x, L.tm_qkv, L.tm2_qkv, h->qkv, L.bqkv, nullptr, 3 * H, H, 3 * H, 0,
+                          GEMM_EPI_BIAS))) {
       return rc;
+    }
     mark(h, K_ATTENTION);
     if ((rc = attention_bf16(st, h->tm_att, h->ctx, h->lens, B, S, H, cu))) return rc;
     if (l + 1 == m.layers) {
@@ -427,7 +492,11 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
       // row-wise, so run them on the B gathered rows; per-row results are unchanged
       mark(h, K_GEMM_OUT);
       if ((rc = gather_cls_rows(st, h->ctx, cu, S, B, H, h->cls_ctx))) return rc;
-      if ((rc = gather_cls_rows(st, h->x, cu, S, B, H, h->cls))) return rc;
+      if (fold) {
+        if ((rc = gather_cls_rows_norm(st, h->x, in_stats, in_g, in_b, cu, S, B, H, h->cls))) return rc;
+      } else if ((rc = gather_cls_rows(st, h->x, cu, S, B, H, h->cls))) {
+        return rc;
+      }
       if ((rc = gemm_bf16_tn(st, h->tm_cls_ctx, L.tm_o, h->cls_y, L.bo, h->cls, B, H, H, H, H,
                              GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
       mark(h, K_LAYERNORM);
@@ -442,6 +511,30 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
       if ((rc = layernorm_inplace(st, h->cls, L.ln2_g, L.ln2_b, m.ln_eps, B, H))) return rc;
       *launches += 9;
       break;
+    }
+    if (fold) {
+      GemmLnArgs a;
+      mark(h, K_GEMM_OUT);
+      a.row_stats = in_stats; a.res_gamma = in_g; a.res_beta = in_b;
+      a.part_out = h->part; a.part_slots = h->part_slots;
+      if ((rc = gemm_ln(h->tm_ctx, L.tm2_o, h->y, L.bo, h->x, H, H, H, H, GEMM_EPI_LNRES_STATS, a))) return rc;
+      mark(h, K_LAYERNORM);
+      if ((rc = ln_stats_finalize(st, h->part, h->part_slots, M, H, m.ln_eps, h->stats_a, m_dev))) return rc;
+      mark(h, K_GEMM_FFN1);
+      GemmLnArgs f1;
+      f1.row_stats = h->stats_a; f1.g = L.g_1;
+      if ((rc = gemm_ln(h->tm_y, L.tm2_1_f, h->ffn, L.c_1, nullptr, I, H, I, 0, GEMM_EPI_LNIN_GELU, f1)))
+        return rc;
+      mark(h, K_GEMM_FFN2);
+      GemmLnArgs f2;
+      f2.row_stats = h->stats_a; f2.res_gamma = L.ln1_g; f2.res_beta = L.ln1_b;
+      f2.part_out = h->part; f2.part_slots = h->part_slots;
+      if ((rc = gemm_ln(h->tm_ffn, L.tm2_2, h->x, L.b2, h->y, H, I, H, H, GEMM_EPI_LNRES_STATS, f2))) return rc;
+      mark(h, K_LAYERNORM);
+      if ((rc = ln_stats_finalize(st, h->part, h->part_slots, M, H, m.ln_eps, h->stats_b, m_dev))) return rc;
+      in_stats = h->stats_b; in_g = L.ln2_g; in_b = L.ln2_b;
+      *launches += 7;
+      continue;
     }
     mark(h, K_GEMM_OUT);
     if ((rc = gemm(h->tm_ctx, L.tm_o, L.tm2_o, h->y, L.bo, h->x, H, H, H, H, GEMM_EPI_BIAS_RESIDUAL)))
@@ -665,6 +758,8 @@ int b2_create(const b2_config* cfg, b2_handle** out) {
   h->packed = !(padded_env && padded_env[0] == '1');
   const char* one_cta_env = getenv("B2_GEMM_1CTA");
   h->pair_gemm = !(one_cta_env && one_cta_env[0] == '1');
+  const char* no_fold_env = getenv("B2_NO_LN_FOLD");
+  h->fold_ln = !(no_fold_env && no_fold_env[0] == '1');
   if (h->max_batch > 4096) {
     set_last_error("b2_create: max_batch %d exceeds 4096", h->max_batch);
     delete h;
@@ -725,6 +820,7 @@ int b2_get_model_info(b2_handle* h, b2_model_info* out) {
   out->sm_count = h->num_sms;
   out->weight_bytes = h->weight_bytes; out->activation_bytes = h->activation_bytes;
   out->packed_rows = h->packed ? 1 : 0;
+  out->ln_folded = h->fold_ln ? 1 : 0;
   return B2_OK;
 }
 

@@ -95,7 +95,7 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank)
 
 template <int EPI>
 __device__ __forceinline__ float epi_act(float v) {
-  if (EPI == GEMM_EPI_BIAS_GELU) return gelu_erf(v);
+  if (EPI == GEMM_EPI_BIAS_GELU || EPI == GEMM_EPI_LNIN_GELU) return gelu_erf(v);
   if (EPI == GEMM_EPI_BIAS_TANH) return tanhf(v);
   return v;
 }
@@ -105,8 +105,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
 gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
                      const __grid_constant__ CUtensorMap tmap_b, __nv_bfloat16* __restrict__ C,
                      const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
-                     int M, int N, int K, int ldc, int ldr, const int32_t* __restrict__ m_dev) {
+                     int M, int N, int K, int ldc, int ldr, const int32_t* __restrict__ m_dev,
+                     const GemmLnArgs ln) {
   extern __shared__ uint8_t smem_raw[];
+  constexpr bool kLnIn = EPI == GEMM_EPI_LNIN || EPI == GEMM_EPI_LNIN_GELU;
+  constexpr bool kLnRes = EPI == GEMM_EPI_LNRES_STATS;
+  constexpr bool kResidual = EPI == GEMM_EPI_BIAS_RESIDUAL || kLnRes;
   if (m_dev) M = min(M, __ldg(m_dev));
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -215,7 +219,10 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int colq = n_blk * BN + quarter * 64;
       __nv_bfloat16* crow = C + static_cast<size_t>(row) * ldc;
       uint4 res[8];
-      if (EPI == GEMM_EPI_BIAS_RESIDUAL) {
+      float2 st = make_float2(0.f, 1.f);  // (mean, rstd) of this row
+      if (kLnIn || kLnRes) st = row_ok ? __ldg(ln.row_stats + row) : st;
+      float psum = 0.f, psq = 0.f;
+      if (kResidual) {
         const __nv_bfloat16* rrow = residual + static_cast<size_t>(row) * ldr;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -247,12 +254,44 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
             v[5] = __uint_as_float(r[j * 8 + 5]) + b1.y;
             v[6] = __uint_as_float(r[j * 8 + 6]) + b1.z;
             v[7] = __uint_as_float(r[j * 8 + 7]) + b1.w;
+            if (kLnIn) {
+              // acc·r − μ·r·g + c   (b0/b1 above carried c; undo the plain add)
+              const float4 g0 = __ldg(reinterpret_cast<const float4*>(ln.g + col));
+              const float4 g1 = __ldg(reinterpret_cast<const float4*>(ln.g + col + 4));
+              const float mr = st.x * st.y;
+              v[0] = fmaf(__uint_as_float(r[j * 8 + 0]), st.y, fmaf(-mr, g0.x, b0.x));
+              v[1] = fmaf(__uint_as_float(r[j * 8 + 1]), st.y, fmaf(-mr, g0.y, b0.y));
+              v[2] = fmaf(__uint_as_float(r[j * 8 + 2]), st.y, fmaf(-mr, g0.z, b0.z));
+              v[3] = fmaf(__uint_as_float(r[j * 8 + 3]), st.y, fmaf(-mr, g0.w, b0.w));
+              v[4] = fmaf(__uint_as_float(r[j * 8 + 4]), st.y, fmaf(-mr, g1.x, b1.x));
+              v[5] = fmaf(__uint_as_float(r[j * 8 + 5]), st.y, fmaf(-mr, g1.y, b1.y));
+              v[6] = fmaf(__uint_as_float(r[j * 8 + 6]), st.y, fmaf(-mr, g1.z, b1.z));
+              v[7] = fmaf(__uint_as_float(r[j * 8 + 7]), st.y, fmaf(-mr, g1.w, b1.w));
+            }
             if (EPI == GEMM_EPI_BIAS_RESIDUAL) {
               const uint4 rv = res[c * 4 + j];
               v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x);
               v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
               v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z);
               v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
+            }
+            if (kLnRes) {
+              // residual = LayerNorm(U) rebuilt from the un-normalised row: (U − μ)·r·γ + β
+              const uint4 rv = res[c * 4 + j];
+              const float4 ga0 = __ldg(reinterpret_cast<const float4*>(ln.res_gamma + col));
+              const float4 ga1 = __ldg(reinterpret_cast<const float4*>(ln.res_gamma + col + 4));
+              const float4 be0 = __ldg(reinterpret_cast<const float4*>(ln.res_beta + col));
+              const float4 be1 = __ldg(reinterpret_cast<const float4*>(ln.res_beta + col + 4));
+              v[0] += fmaf((bf16_lo(rv.x) - st.x) * st.y, ga0.x, be0.x);
+              v[1] += fmaf((bf16_hi(rv.x) - st.x) * st.y, ga0.y, be0.y);
+              v[2] += fmaf((bf16_lo(rv.y) - st.x) * st.y, ga0.z, be0.z);
+              v[3] += fmaf((bf16_hi(rv.y) - st.x) * st.y, ga0.w, be0.w);
+              v[4] += fmaf((bf16_lo(rv.z) - st.x) * st.y, ga1.x, be1.x);
+              v[5] += fmaf((bf16_hi(rv.z) - st.x) * st.y, ga1.y, be1.y);
+              v[6] += fmaf((bf16_lo(rv.w) - st.x) * st.y, ga1.z, be1.z);
+              v[7] += fmaf((bf16_hi(rv.w) - st.x) * st.y, ga1.w, be1.w);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) { psum += v[e]; psq = fmaf(v[e], v[e], psq); }
             }
 #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] = epi_act<EPI>(v[e]);
@@ -265,6 +304,8 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         }
       }
+      if (kLnRes && row_ok && colq < N)
+        ln.part_out[static_cast<size_t>(row) * ln.part_slots + (colq >> 6)] = make_float2(psum, psq);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);  // the issuer waits on the leader's copy
@@ -283,7 +324,7 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
 template <int EPI>
 int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, __nv_bfloat16* C,
             const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int ldc, int ldr,
-            int num_sms, const int32_t* m_dev) {
+            int num_sms, const int32_t* m_dev, const GemmLnArgs& ln) {
   static bool configured[64] = {};
   int dev = 0;
   B2_CUDA_OK(cudaGetDevice(&dev));
@@ -296,7 +337,7 @@ int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, _
   int pairs = num_sms / 2;
   if (tiles < pairs) pairs = tiles;
   gemm2_bf16_tn_kernel<EPI><<<2 * pairs, THREADS, SMEM_BYTES, stream>>>(ta, tb, C, bias, residual, M, N,
-                                                                       K, ldc, ldr, m_dev);
+                                                                       K, ldc, ldr, m_dev, ln);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }
@@ -310,7 +351,9 @@ int gemm2_tmap_b(CUtensorMap* out, const void* W, int N, int K) {
 
 int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb,
                   __nv_bfloat16* C, const float* bias, const __nv_bfloat16* residual, int M, int N,
-                  int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev) {
+                  int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev,
+                  const GemmLnArgs* ln_in) {
+  const GemmLnArgs ln = ln_in ? *ln_in : GemmLnArgs();
   if (M <= 0 || N <= 0 || K <= 0 || (N % 8) != 0 || (K % 8) != 0 || (ldc % 8) != 0 || num_sms < 2) {
     set_last_error("gemm2_bf16_tn: bad shape M=%d N=%d K=%d ldc=%d (N, K, ldc must be multiples of 8)",
                    M, N, K, ldc);
@@ -318,20 +361,40 @@ int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap&
   }
   switch (epilogue) {
     case GEMM_EPI_BIAS:
-      return launch2<GEMM_EPI_BIAS>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms, m_dev);
+      return launch2<GEMM_EPI_BIAS>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms, m_dev, ln);
     case GEMM_EPI_BIAS_GELU:
       return launch2<GEMM_EPI_BIAS_GELU>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms,
-                                         m_dev);
+                                         m_dev, ln);
     case GEMM_EPI_BIAS_RESIDUAL:
       if (!residual || (ldr % 8) != 0) {
         set_last_error("gemm2_bf16_tn: residual epilogue needs a residual pointer and ldr %% 8 == 0");
         return B2_ERR_ARG;
       }
       return launch2<GEMM_EPI_BIAS_RESIDUAL>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr,
-                                             num_sms, m_dev);
+                                             num_sms, m_dev, ln);
     case GEMM_EPI_BIAS_TANH:
       return launch2<GEMM_EPI_BIAS_TANH>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms,
-                                         m_dev);
+                                         m_dev, ln);
+  }
+  if (epilogue == GEMM_EPI_LNIN || epilogue == GEMM_EPI_LNIN_GELU) {
+    if (!ln.row_stats || !ln.g) {
+      set_last_error("gemm2_bf16_tn: LNIN epilogue needs row_stats and g");
+      return B2_ERR_ARG;
+    }
+    return epilogue == GEMM_EPI_LNIN
+               ? launch2<GEMM_EPI_LNIN>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms, m_dev, ln)
+               : launch2<GEMM_EPI_LNIN_GELU>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms,
+                                             m_dev, ln);
+  }
+  if (epilogue == GEMM_EPI_LNRES_STATS) {
+    if (!residual || (ldr % 8) != 0 || !ln.row_stats || !ln.res_gamma || !ln.res_beta || !ln.part_out ||
+        ln.part_slots * 64 < N) {
+      set_last_error("gemm2_bf16_tn: LNRES_STATS epilogue needs residual, row_stats, gamma, beta and "
+                     "part_out with part_slots >= N/64");
+      return B2_ERR_ARG;
+    }
+    return launch2<GEMM_EPI_LNRES_STATS>(stream, ta, tb, C, bias, residual, M, N, K, ldc, ldr, num_sms,
+                                         m_dev, ln);
   }
   set_last_error("gemm2_bf16_tn: unknown epilogue %d", epilogue);
   return B2_ERR_ARG;

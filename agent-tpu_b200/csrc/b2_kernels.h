@@ -11,6 +11,23 @@ enum GemmEpilogue {
   GEMM_EPI_BIAS_GELU = 1,      // C = gelu_erf(A·Wᵀ + b)
   GEMM_EPI_BIAS_RESIDUAL = 2,  // C = A·Wᵀ + b + R
   GEMM_EPI_BIAS_TANH = 3,      // C = tanh(A·Wᵀ + b)      (pooler)
+  // LayerNorm folded into the GEMMs around it (pair kernel only, see GemmLnArgs):
+  GEMM_EPI_LNIN = 4,           // C = r[m]·(A·W'ᵀ − μ[m]·g) + c            A holds un-normalised rows
+  GEMM_EPI_LNIN_GELU = 5,      // C = gelu_erf(r[m]·(A·W'ᵀ − μ[m]·g) + c)
+  GEMM_EPI_LNRES_STATS = 6,    // C = A·Wᵀ + b + ((U − μ)·r·γ + β); per-row Σ, Σ² of C -> part_out
+};
+// Arguments of the LayerNorm-folding epilogues. With x = (U − μ)·r·γ + β never materialised:
+//   x·Wᵀ + b = r·(U·(γ∘W)ᵀ − μ·g) + c,   g[n] = Σ_k (γ∘W)[n,k],   c[n] = b[n] + Σ_k β[k]·W[n,k]
+// so a GEMM can consume the un-normalised rows U directly (LNIN), and the residual add of the
+// GEMM that closes a sub-layer can rebuild x from U on the fly while it emits the row sums the next
+// LayerNorm needs (LNRES_STATS). Row statistics travel as float2 (mean, rstd) per row.
+struct GemmLnArgs {
+  const float2* row_stats = nullptr;  // LNIN: stats of A's rows. LNRES: stats of the residual rows U
+  const float* g = nullptr;           // LNIN: column sums of the folded weight (bias slot carries c)
+  const float* res_gamma = nullptr;   // LNRES: γ, β of the LayerNorm that produces the residual
+  const float* res_beta = nullptr;
+  float2* part_out = nullptr;         // LNRES: [rows, part_slots] partial (Σ, Σ²), slot = column/64
+  int part_slots = 0;
 };
 // Tensor maps: A is [M,K] bf16 with row pitch lda elements, W is [N,K] bf16 dense.
 int gemm_tmap_a(CUtensorMap* out, const void* A, int M, int K, int64_t lda);
@@ -25,7 +42,8 @@ int gemm_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& 
 int gemm2_tmap_b(CUtensorMap* out, const void* W, int N, int K);
 int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb,
                   __nv_bfloat16* C, const float* bias, const __nv_bfloat16* residual, int M, int N,
-                  int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev = nullptr);
+                  int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev = nullptr,
+                  const GemmLnArgs* ln = nullptr);
 
 // ---- attention (b2_attention.cu) ---------------------------------------------------------------
 // qkv: [rows, 3*H] bf16 (Q | K | V per token row, head h at columns h*64), out: [rows, H] bf16.
@@ -50,6 +68,16 @@ int embed_layernorm(cudaStream_t stream, const int32_t* ids, const float* word, 
 // x[row] = LayerNorm(x[row]) * gamma + beta   (in place, bf16 storage, f32 math)
 int layernorm_inplace(cudaStream_t stream, __nv_bfloat16* x, const float* gamma, const float* beta,
                       float eps, int rows, int hidden, const int32_t* rows_dev = nullptr);
+// stats[row] = (mean, rsqrt(var + eps)) from the partial sums a GEMM_EPI_LNRES_STATS epilogue wrote;
+// partials are added in slot order, so the result does not depend on scheduling.
+int ln_stats_finalize(cudaStream_t stream, const float2* part, int slots, int rows, int hidden, float eps,
+                      float2* stats, const int32_t* rows_dev = nullptr);
+// stats[row] = (0, 1): rows that are already normalised (the embedding output)
+int ln_stats_identity(cudaStream_t stream, float2* stats, int rows);
+// dst[b,:] = (src[first row of sequence b,:] − μ)·r·γ + β   (gather the [CLS] rows and normalise them)
+int gather_cls_rows_norm(cudaStream_t stream, const __nv_bfloat16* src, const float2* stats,
+                         const float* gamma, const float* beta, const int32_t* cu, int S, int B, int hidden,
+                         __nv_bfloat16* dst);
 // cu[0..B] = exclusive prefix sum of lens, cu[B] = total rows (also the GEMMs' m_dev); B <= 4096.
 int pack_offsets(cudaStream_t stream, const int32_t* lens, int B, int32_t* cu);
 // dst[b, :] = src[first row of sequence b, :]  (the [CLS] rows): row cu[b] (packed) or b*S (cu null)
@@ -70,5 +98,9 @@ int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B,
 int fill_synthetic_f32(cudaStream_t stream, float* dst, int64_t n, uint64_t seed,
                        uint32_t tensor_id, float scale, float shift);
 int convert_f32_to_bf16(cudaStream_t stream, const float* src, __nv_bfloat16* dst, int64_t n);
+// Fold a LayerNorm's affine into the Linear that follows it: Wf[n,k] = bf16(gamma[k]·W[n,k]),
+// g[n] = Σ_k float(Wf[n,k]), c[n] = bias[n] + Σ_k beta[k]·W[n,k]. gamma/beta null = identity.
+int fold_ln_into_linear(cudaStream_t stream, const float* W, const float* bias, const float* gamma,
+                        const float* beta, int N, int K, __nv_bfloat16* Wf, float* g, float* c);
 
 }  // namespace b2

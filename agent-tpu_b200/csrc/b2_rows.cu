@@ -240,6 +240,48 @@ __global__ void gather_cls_kernel(const __nv_bfloat16* __restrict__ src, const i
   for (int i = threadIdx.x; i < hidden / 4; i += blockDim.x) d[i] = s[i];
 }
 
+// ---- LayerNorm statistics for the folded path ---------------------------------------------------
+__global__ void ln_stats_finalize_kernel(const float2* __restrict__ part, int slots, int rows, float inv_h,
+                                         float eps, float2* __restrict__ stats,
+                                         const int32_t* __restrict__ rows_dev) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (rows_dev) rows = min(rows, __ldg(rows_dev));
+  if (row >= rows) return;
+  const float2* p = part + static_cast<size_t>(row) * slots;
+  float s = 0.f, q = 0.f;
+  for (int i = 0; i < slots; ++i) {  // fixed order: the sums are reproducible
+    const float2 v = p[i];
+    s += v.x;
+    q += v.y;
+  }
+  const float mean = s * inv_h;
+  const float var = fmaxf(q * inv_h - mean * mean, 0.f);
+  stats[row] = make_float2(mean, rsqrtf(var + eps));
+}
+
+__global__ void ln_stats_identity_kernel(float2* __restrict__ stats, int rows) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row < rows) stats[row] = make_float2(0.f, 1.f);
+}
+
+__global__ void gather_cls_norm_kernel(const __nv_bfloat16* __restrict__ src, const float2* __restrict__ stats,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       const int32_t* __restrict__ cu, int S, int B, int hidden,
+                                       __nv_bfloat16* __restrict__ dst) {
+  const int b = blockIdx.x;
+  if (b >= B) return;
+  const size_t row = cu ? static_cast<size_t>(cu[b]) : static_cast<size_t>(b) * S;
+  const float2 st = stats[row];
+  const __nv_bfloat16* s = src + row * hidden;
+  __nv_bfloat16* d = dst + static_cast<size_t>(b) * hidden;
+  for (int c = threadIdx.x * 2; c < hidden; c += blockDim.x * 2) {
+    const uint32_t raw = *reinterpret_cast<const uint32_t*>(s + c);
+    const float a = fmaf((bf16_lo(raw) - st.x) * st.y, gamma[c], beta[c]);
+    const float e = fmaf((bf16_hi(raw) - st.x) * st.y, gamma[c + 1], beta[c + 1]);
+    *reinterpret_cast<uint32_t*>(d + c) = pack_bf16x2(a, e);
+  }
+}
+
 __global__ void mask_to_lens_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ lens,
                                     int B, int S) {
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -315,6 +357,31 @@ int gather_cls_rows(cudaStream_t stream, const __nv_bfloat16* src, const int32_t
                     int hidden, __nv_bfloat16* dst) {
   if (B <= 0) return B2_OK;
   gather_cls_kernel<<<B, 128, 0, stream>>>(src, cu, S, B, hidden, dst);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int ln_stats_finalize(cudaStream_t stream, const float2* part, int slots, int rows, int hidden, float eps,
+                      float2* stats, const int32_t* rows_dev) {
+  if (rows <= 0) return B2_OK;
+  ln_stats_finalize_kernel<<<(rows + 255) / 256, 256, 0, stream>>>(part, slots, rows, 1.0f / hidden, eps,
+                                                                    stats, rows_dev);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int ln_stats_identity(cudaStream_t stream, float2* stats, int rows) {
+  if (rows <= 0) return B2_OK;
+  ln_stats_identity_kernel<<<(rows + 255) / 256, 256, 0, stream>>>(stats, rows);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int gather_cls_rows_norm(cudaStream_t stream, const __nv_bfloat16* src, const float2* stats,
+                         const float* gamma, const float* beta, const int32_t* cu, int S, int B, int hidden,
+                         __nv_bfloat16* dst) {
+  if (B <= 0) return B2_OK;
+  gather_cls_norm_kernel<<<B, 128, 0, stream>>>(src, stats, gamma, beta, cu, S, B, hidden, dst);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }

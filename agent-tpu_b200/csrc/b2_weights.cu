@@ -38,7 +38,43 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16*
     dst[i] = __float2bfloat16_rn(src[i]);
 }
 
+// one warp per output row n of W[N,K]
+__global__ void fold_ln_kernel(const float* __restrict__ W, const float* __restrict__ bias,
+                               const float* __restrict__ gamma, const float* __restrict__ beta, int N, int K,
+                               __nv_bfloat16* __restrict__ Wf, float* __restrict__ g, float* __restrict__ c) {
+  const int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (n >= N) return;
+  const int lane = threadIdx.x & 31;
+  const float* w = W + static_cast<size_t>(n) * K;
+  __nv_bfloat16* wf = Wf + static_cast<size_t>(n) * K;
+  float gs = 0.f, cs = 0.f;
+  for (int k = lane; k < K; k += 32) {
+    const float wk = w[k];
+    const __nv_bfloat16 f = __float2bfloat16_rn(gamma ? gamma[k] * wk : wk);
+    wf[k] = f;
+    gs += __bfloat162float(f);  // the sum of what the tensor core will actually multiply
+    if (beta) cs = fmaf(beta[k], wk, cs);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    gs += __shfl_xor_sync(0xffffffffu, gs, o);
+    cs += __shfl_xor_sync(0xffffffffu, cs, o);
+  }
+  if (lane == 0) {
+    g[n] = gs;
+    c[n] = bias[n] + cs;
+  }
+}
+
 }  // namespace
+
+int fold_ln_into_linear(cudaStream_t stream, const float* W, const float* bias, const float* gamma,
+                        const float* beta, int N, int K, __nv_bfloat16* Wf, float* g, float* c) {
+  if (N <= 0 || K <= 0) return B2_OK;
+  fold_ln_kernel<<<(N + 7) / 8, 256, 0, stream>>>(W, bias, gamma, beta, N, K, Wf, g, c);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
 
 int fill_synthetic_f32(cudaStream_t stream, float* dst, int64_t n, uint64_t seed,
                        uint32_t tensor_id, float scale, float shift) {

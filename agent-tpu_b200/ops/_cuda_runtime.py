@@ -55,7 +55,7 @@ class ModelInfo(C.Structure):
                                          "max_positions", "num_labels", "tokenizer_vocab_size",
                                          "max_batch", "max_len", "device", "sm_count")] + \
                [("weight_bytes", C.c_int64), ("activation_bytes", C.c_int64), ("packed_rows", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("ln_folded", C.c_int32)]
 
 
 _METRIC_KINDS = ("tokenize", "embed", "gemm_qkv", "attention", "gemm_attn_out", "layernorm", "gemm_ffn1",

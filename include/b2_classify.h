@@ -50,7 +50,7 @@ typedef struct b2_model_info {
   int32_t max_batch, max_len, device, sm_count;
   int64_t weight_bytes, activation_bytes;
   int32_t packed_rows; /* 1: padding-free token rows (default); 0: B2_FORCE_PADDED=1 was set */
-  int32_t reserved;
+  int32_t ln_folded;   /* 1: LayerNorms folded into the GEMM epilogues (default); 0: B2_NO_LN_FOLD=1 */
 } b2_model_info;
 
 /* Per-call counters and device timings (CUDA events on the library's stream). The reference

@@ -139,6 +139,31 @@ def test_packed_rows_equal_padded_rows_bit_for_bit(tiny_model, vocab_path, sente
         a.close(); b.close()
 
 
+def test_folded_layernorm_agrees_with_explicit_layernorm(base_model, vocab_path, sentences, monkeypatch):
+    """LayerNorm folded into the GEMM epilogues (default) against B2_NO_LN_FOLD=1, which runs the
+    LayerNorm kernels: two roundings of the same network, so close but not bit-identical, and both
+    inside the stated tolerance of the fp32 oracle."""
+    import bert_oracle as bo
+    from ops import _cuda_runtime as rt
+    texts = sentences[300:364]
+    a = rt.Engine(base_model, vocab_path, max_batch=64, max_len=128)
+    monkeypatch.setenv("B2_NO_LN_FOLD", "1")
+    b = rt.Engine(base_model, vocab_path, max_batch=64, max_len=128)
+    monkeypatch.delenv("B2_NO_LN_FOLD")
+    try:
+        assert a.info.ln_folded == 1 and b.info.ln_folded == 0
+        oa = a.classify(texts, 128, 5, want_logits=True)
+        ob = b.classify(texts, 128, 5, want_logits=True)
+    finally:
+        a.close(); b.close()
+    cfg, W = bo.load_model(base_model)
+    ids, mask = bo.tokenize(vocab_path, texts, 128)
+    ref = bo.forward(cfg, W, ids, mask)
+    ea, eb = np.abs(oa["logits"] - ref).max(), np.abs(ob["logits"] - ref).max()
+    assert ea <= LOGIT_TOL and eb <= LOGIT_TOL, (ea, eb)
+    assert np.abs(oa["logits"] - ob["logits"]).max() <= LOGIT_TOL
+
+
 def test_ids_entry_point_equals_text_entry_point(tiny_engine, sentences):
     texts = sentences[:70]
     ids, mask, _ = tiny_engine.tokenize(texts, 128)
