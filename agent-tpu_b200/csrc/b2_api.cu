@@ -129,7 +129,8 @@ struct b2_handle {
   uint8_t* mask = nullptr;
   __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *ffn = nullptr,
                 *pooled = nullptr;
-  CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{};
+  CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{};  // A operands; also TMA store / residual maps
+  CUtensorMap tm_qkv_c{};                          // qkv as a GEMM output
   AttentionMaps tm_att{};
   unsigned long long* hist = nullptr;
   int64_t* d_tokens = nullptr;  // running sum of lens
@@ -409,6 +410,7 @@ int alloc_activations(b2_handle* h) {
   if ((rc = gemm_tmap_a(&h->tm_ctx, h->ctx, rows, H, H))) return rc;
   if ((rc = gemm_tmap_a(&h->tm_y, h->y, rows, H, H))) return rc;
   if ((rc = gemm_tmap_a(&h->tm_ffn, h->ffn, rows, I, I))) return rc;
+  if ((rc = gemm2_tmap_c(&h->tm_qkv_c, h->qkv, rows, 3 * H, 3 * H))) return rc;
   if ((rc = attention_tmaps(&h->tm_att, h->qkv, rows, H))) return rc;
   B2_CUDA_OK(cudaStreamSynchronize(h->stream));
   return B2_OK;
@@ -453,9 +455,10 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
   ++*launches;
   // encoder projections: CTA-pair kernel when the batch is large enough to fill 74 pairs
   const bool pair = h->pair_gemm && M >= 4096;
-  auto gemm = [&](const CUtensorMap& ta, const CUtensorMap& tb1, const CUtensorMap& tb2, __nv_bfloat16* Cc,
-                  const float* bias, const __nv_bfloat16* res, int N, int K, int ldc, int ldr, int epi) {
-    return pair ? gemm2_bf16_tn(st, ta, tb2, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev)
+  auto gemm = [&](const CUtensorMap& ta, const CUtensorMap& tb1, const CUtensorMap& tb2, const CUtensorMap& tc,
+                  __nv_bfloat16* Cc, const float* bias, const CUtensorMap* tr, const __nv_bfloat16* res, int N,
+                  int K, int ldc, int ldr, int epi) {
+    return pair ? gemm2_bf16_tn(st, ta, tb2, tc, tr, bias, M, N, K, epi, h->num_sms, m_dev)
                 : gemm_bf16_tn(st, ta, tb1, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev);
   };
   const bool fold = h->fold_ln;
@@ -468,9 +471,9 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
     if ((rc = ln_stats_identity(st, h->stats_b, M))) return rc;  // the embedding output is normalised
     ++*launches;
   }
-  auto gemm_ln = [&](const CUtensorMap& ta, const CUtensorMap& tb, __nv_bfloat16* Cc, const float* bias,
-                     const __nv_bfloat16* res, int N, int K, int ldc, int ldr, int epi, const GemmLnArgs& a) {
-    return gemm2_bf16_tn(st, ta, tb, Cc, bias, res, M, N, K, ldc, ldr, epi, h->num_sms, m_dev, &a);
+  auto gemm_ln = [&](const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias,
+                     const CUtensorMap* tr, int N, int K, int epi, const GemmLnArgs& a) {
+    return gemm2_bf16_tn(st, ta, tb, tc, tr, bias, M, N, K, epi, h->num_sms, m_dev, &a);
   };
   for (uint32_t l = 0; l < m.layers; ++l) {
     LayerWeights& L = h->layers[l];
@@ -479,10 +482,10 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
       GemmLnArgs a;
       a.row_stats = in_stats;
       a.g = L.g_qkv;
-      if ((rc = gemm_ln(h->tm_x, L.tm2_qkv_f, h->qkv, L.c_qkv, nullptr, 3 * H, H, 3 * H, 0, GEMM_EPI_LNIN, a)))
+      if ((rc = gemm_ln(h->tm_x, L.tm2_qkv_f, h->tm_qkv_c, L.c_qkv, nullptr, 3 * H, H, GEMM_EPI_LNIN, a)))
         return rc;
-    } else if ((rc = gemm(h->tm_x, L.tm_qkv, L.tm2_qkv, h->qkv, L.bqkv, nullptr, 3 * H, H, 3 * H, 0,
-                          GEMM_EPI_BIAS))) {
+    } else if ((rc = gemm(h->tm_x, L.tm_qkv, L.tm2_qkv, h->tm_qkv_c, h->qkv, L.bqkv, nullptr, nullptr, 3 * H, H,
+                          3 * H, 0, GEMM_EPI_BIAS))) {
       return rc;
     }
     mark(h, K_ATTENTION);
@@ -517,19 +520,19 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
       mark(h, K_GEMM_OUT);
       a.row_stats = in_stats; a.res_gamma = in_g; a.res_beta = in_b;
       a.part_out = h->part; a.part_slots = h->part_slots;
-      if ((rc = gemm_ln(h->tm_ctx, L.tm2_o, h->y, L.bo, h->x, H, H, H, H, GEMM_EPI_LNRES_STATS, a))) return rc;
+      if ((rc = gemm_ln(h->tm_ctx, L.tm2_o, h->tm_y, L.bo, &h->tm_x, H, H, GEMM_EPI_LNRES_STATS, a))) return rc;
       mark(h, K_LAYERNORM);
       if ((rc = ln_stats_finalize(st, h->part, h->part_slots, M, H, m.ln_eps, h->stats_a, m_dev))) return rc;
       mark(h, K_GEMM_FFN1);
       GemmLnArgs f1;
       f1.row_stats = h->stats_a; f1.g = L.g_1;
-      if ((rc = gemm_ln(h->tm_y, L.tm2_1_f, h->ffn, L.c_1, nullptr, I, H, I, 0, GEMM_EPI_LNIN_GELU, f1)))
+      if ((rc = gemm_ln(h->tm_y, L.tm2_1_f, h->tm_ffn, L.c_1, nullptr, I, H, GEMM_EPI_LNIN_GELU, f1)))
         return rc;
       mark(h, K_GEMM_FFN2);
       GemmLnArgs f2;
       f2.row_stats = h->stats_a; f2.res_gamma = L.ln1_g; f2.res_beta = L.ln1_b;
       f2.part_out = h->part; f2.part_slots = h->part_slots;
-      if ((rc = gemm_ln(h->tm_ffn, L.tm2_2, h->x, L.b2, h->y, H, I, H, H, GEMM_EPI_LNRES_STATS, f2))) return rc;
+      if ((rc = gemm_ln(h->tm_ffn, L.tm2_2, h->tm_x, L.b2, &h->tm_y, H, I, GEMM_EPI_LNRES_STATS, f2))) return rc;
       mark(h, K_LAYERNORM);
       if ((rc = ln_stats_finalize(st, h->part, h->part_slots, M, H, m.ln_eps, h->stats_b, m_dev))) return rc;
       in_stats = h->stats_b; in_g = L.ln2_g; in_b = L.ln2_b;
@@ -537,15 +540,18 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
       continue;
     }
     mark(h, K_GEMM_OUT);
-    if ((rc = gemm(h->tm_ctx, L.tm_o, L.tm2_o, h->y, L.bo, h->x, H, H, H, H, GEMM_EPI_BIAS_RESIDUAL)))
+    if ((rc = gemm(h->tm_ctx, L.tm_o, L.tm2_o, h->tm_y, h->y, L.bo, &h->tm_x, h->x, H, H, H, H,
+                   GEMM_EPI_BIAS_RESIDUAL)))
       return rc;
     mark(h, K_LAYERNORM);
     if ((rc = layernorm_inplace(st, h->y, L.ln1_g, L.ln1_b, m.ln_eps, M, H, m_dev))) return rc;
     mark(h, K_GEMM_FFN1);
-    if ((rc = gemm(h->tm_y, L.tm_1, L.tm2_1, h->ffn, L.b1, nullptr, I, H, I, 0, GEMM_EPI_BIAS_GELU)))
+    if ((rc = gemm(h->tm_y, L.tm_1, L.tm2_1, h->tm_ffn, h->ffn, L.b1, nullptr, nullptr, I, H, I, 0,
+                   GEMM_EPI_BIAS_GELU)))
       return rc;
     mark(h, K_GEMM_FFN2);
-    if ((rc = gemm(h->tm_ffn, L.tm_2, L.tm2_2, h->x, L.b2, h->y, H, I, H, H, GEMM_EPI_BIAS_RESIDUAL)))
+    if ((rc = gemm(h->tm_ffn, L.tm_2, L.tm2_2, h->tm_x, h->x, L.b2, &h->tm_y, h->y, H, I, H, H,
+                   GEMM_EPI_BIAS_RESIDUAL)))
       return rc;
     mark(h, K_LAYERNORM);
     if ((rc = layernorm_inplace(st, h->x, L.ln2_g, L.ln2_b, m.ln_eps, M, H, m_dev))) return rc;

@@ -40,10 +40,13 @@ int gemm_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& 
 // Same contract on CTA pairs (b2_gemm2.cu: cta_group::2, 256 x 256 pair tile). `ta` is the same A map;
 // `tb` must come from gemm2_tmap_b (128-row boxes of W).
 int gemm2_tmap_b(CUtensorMap* out, const void* W, int N, int K);
-int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb,
-                  __nv_bfloat16* C, const float* bias, const __nv_bfloat16* residual, int M, int N,
-                  int K, int ldc, int ldr, int epilogue, int num_sms, const int32_t* m_dev = nullptr,
-                  const GemmLnArgs* ln = nullptr);
+// `tc` (output) and `tr` (residual, may be null) are 128 x 64-box maps of [rows, cols] bf16 buffers
+// (gemm2_tmap_c, same geometry as gemm_tmap_a): the epilogue stores through TMA and fetches the
+// residual through TMA, so rows beyond the buffer and columns beyond N are clipped by hardware.
+int gemm2_tmap_c(CUtensorMap* out, const void* Cbuf, int rows, int cols, int64_t ldc);
+int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+                  const CUtensorMap* tr, const float* bias, int M, int N, int K, int epilogue, int num_sms,
+                  const int32_t* m_dev = nullptr, const GemmLnArgs* ln = nullptr);
 
 // ---- attention (b2_attention.cu) ---------------------------------------------------------------
 // qkv: [rows, 3*H] bf16 (Q | K | V per token row, head h at columns h*64), out: [rows, H] bf16.

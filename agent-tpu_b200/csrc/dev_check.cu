@@ -59,7 +59,10 @@ static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it, b
   CUtensorMap ta, tb;
   B2(gemm_tmap_a(&ta, dA, M, K, K));
   if (pair) B2(gemm2_tmap_b(&tb, dW, N, K)); else B2(gemm_tmap_b(&tb, dW, N, K));
-  auto run = [&]() { return pair ? gemm2_bf16_tn(0, ta, tb, dC, db, dR, M, N, K, N, N, epi, num_sms)
+  CUtensorMap tc, tr;
+  B2(gemm2_tmap_c(&tc, dC, M, N, N));
+  B2(gemm2_tmap_c(&tr, dR, M, N, N));
+  auto run = [&]() { return pair ? gemm2_bf16_tn(0, ta, tb, tc, &tr, db, M, N, K, epi, num_sms)
                                  : gemm_bf16_tn(0, ta, tb, dC, db, dR, M, N, K, N, N, epi, num_sms); };
   B2(run());
   CK(cudaDeviceSynchronize());
