@@ -219,21 +219,20 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return r;
 }
 // BERT's "gelu": x * Phi(x), Phi(x) = 0.5 * (1 + erf(x / sqrt(2)))  (transformers GELUActivation).
-// Phi(-|x|) = 0.5 * erfc(|x|/sqrt(2)) by Abramowitz & Stegun 7.1.26 (|abs error| < 1.5e-7 on erf):
-// one MUFU.RCP, one MUFU.EX2, nine FP32 ops — no slow paths, no branches. libdevice erff (and the
-// IEEE __frcp_rn the first version used) compile to call/branch sequences that left the FFN1
-// epilogue latency-bound at 23% tensor-pipe activity (profiles/r01_ncu_gemm.md).
+// Evaluated as x * sigmoid(2 q(x)) with q(x) = x (c0 + c1 x^2 + c2 x^4) fitted to atanh(erf(x/sqrt2))
+// on [-8, 8]: |gelu_fit - gelu| < 3.0e-5 absolute over all x (checked in fp32 against scipy erf;
+// outside [-8, 8] the sigmoid is exactly 0 or 1 in fp32), far below the bf16 rounding of the
+// result. Ten instructions, two of them MUFU (ex2, rcp), no branches. History: libdevice erff and
+// IEEE division compiled to call/branch sequences that left the FFN1 epilogue latency-bound at 23%
+// tensor-pipe activity; the Abramowitz-Stegun form that replaced them (17 instructions) still made
+// the FFN1 epilogue longer than its K = 768 main loop (profiles/r01_ncu_gemm.md, r01_ncu_gemm2.md).
 __device__ __forceinline__ float gelu_erf(float x) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  const float t = rcp_approx(fmaf(0.3275911f, z, 1.0f));
-  float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);  // coefficients pre-halved
-  p = fmaf(p, t, 0.5f * 1.421413741f);
-  p = fmaf(p, t, 0.5f * -0.284496736f);
-  p = fmaf(p, t, 0.5f * 0.254829592f);
-  const float e = ex2_approx(z * z * -1.4426950408889634f);
-  const float h = p * t * e;                 // Phi(-|x|)
-  const float phi = x >= 0.f ? 1.0f - h : h;
-  return x * phi;
+  const float xc = fminf(fmaxf(x, -8.0f), 8.0f);
+  const float x2 = xc * xc;
+  float p = fmaf(x2, 0.0010350828524678946f, -0.10690470039844513f);
+  p = fmaf(x2, p, -2.300978660583496f);            // -2 log2(e) q(x) / x
+  const float e = ex2_approx(xc * p);              // exp(-2 q(x))
+  return x * rcp_approx(1.0f + e);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
