@@ -373,18 +373,29 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       const uint32_t tS = tmem_base + s * 128 + lane_base;
       mbar_wait(bar(S_FULL, s), ph);
       tc_fence_after();
+      // A chunk of 32 keys that lies wholly inside the sequence takes the unmasked path: three-input
+      // max (FMNMX3), packed FFMA2 / FADD2, two MUFU.EX2 and one bf16x2 convert per key pair. Only the
+      // one chunk that straddles `len` pays for per-key masking.
       float mx = -INFINITY;
       for (int c = 0; c < 4; ++c) {
         if (c * 32 < len) {
           uint32_t v[32];
           tmem_ld_32x32(tS + c * 32, v);
           tmem_ld_wait();
+          if (c * 32 + 32 <= len) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c * 32 + j < len) mx = fmaxf(mx, __uint_as_float(v[j]));
+            for (int j = 0; j < 32; j += 2)
+              mx = fmaxf(mx, fmaxf(__uint_as_float(v[j]), __uint_as_float(v[j + 1])));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (c * 32 + j < len) mx = fmaxf(mx, __uint_as_float(v[j]));
+          }
         }
       }
       const float moff = mx * sl2;
+      const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
+      uint64_t sum2 = f32x2(0.f, 0.f);
       float rowsum = 0.f;
       for (int c = 0; c < 4; ++c) {
         if (c * 32 < len) {
@@ -392,12 +403,24 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
           uint32_t v[32];
           tmem_ld_32x32(tS + c * 32, v);
           tmem_ld_wait();
+          if (c * 32 + 32 <= len) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            const float p0 = (c * 32 + j < len) ? ex2_approx(fmaf(__uint_as_float(v[j]), sl2, -moff)) : 0.f;
-            const float p1 = (c * 32 + j + 1 < len) ? ex2_approx(fmaf(__uint_as_float(v[j + 1]), sl2, -moff)) : 0.f;
-            rowsum += p0 + p1;
-            packed[j >> 1] = pack_bf16x2(p0, p1);
+            for (int j = 0; j < 32; j += 2) {
+              float p0, p1;
+              f32x2_split(ffma2(f32x2_bits(v[j], v[j + 1]), scale2, shift2), p0, p1);
+              p0 = ex2_approx(p0);
+              p1 = ex2_approx(p1);
+              sum2 = fadd2(sum2, f32x2(p0, p1));
+              packed[j >> 1] = pack_bf16x2(p0, p1);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float p0 = (c * 32 + j < len) ? ex2_approx(fmaf(__uint_as_float(v[j]), sl2, -moff)) : 0.f;
+              const float p1 = (c * 32 + j + 1 < len) ? ex2_approx(fmaf(__uint_as_float(v[j + 1]), sl2, -moff)) : 0.f;
+              rowsum += p0 + p1;
+              packed[j >> 1] = pack_bf16x2(p0, p1);
+            }
           }
           uint8_t* tile = smem_aligned + s * STAGE_BYTES_P + (c >> 1) * TILE_BYTES + r * 128;
 #pragma unroll
@@ -407,6 +430,11 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
                 make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
           }
         }
+      }
+      {
+        float s0, s1;
+        f32x2_split(sum2, s0, s1);
+        rowsum += s0 + s1;
       }
       fence_proxy_async_smem();
       tc_fence_before();
