@@ -375,13 +375,15 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     g_flop = sum(flop.values())
     achieved = g_flop / g_ms / 1e9 if g_ms > 0 else 0.0
     roofline = {
-        "kernel": "gemm_bf16_tn_kernel (tcgen05; QKV, attention-out, FFN1+GELU, FFN2 projections)",
+        "kernel": "gemm2_bf16_tn_kernel (tcgen05 cta_group::2; QKV, attention-out, FFN1+GELU, FFN2 projections)",
         "bound": "tensor", "achieved": round(achieved, 1), "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
         "frac": round(achieved / peaks["bf16_sustained"], 4), "frac_of_burst": round(achieved / peaks["bf16_burst"], 4),
         "peak_source": f"{peaks['source']} bf16_tflops_sustained (kernel timed inside a long step)",
         "flop_per_launch": g_flop / g_n if g_n else None, "avg_launch_ms": g_ms / g_n if g_n else None,
         "launches": g_n, "share_of_step": round(g_ms / (sum(v["ms"] for v in kern.values()) or 1.0), 4),
-        "traffic": None,
+        # dram__bytes_read + write per launch, mean of the four encoder GEMMs in one ncu --set full
+        # capture at T ~ 71K rows per batch (profiles/r01_ncu_gemm2.md); algorithmic bytes are ~equal
+        "traffic": 464.5e6, "traffic_source": "profiles/r01_ncu_gemm2.md (ncu capture r01b, mean of 4 launches)",
     }
     whole = {"achieved_tflops": round(value / world * FLOP_PER_ITEM / 1e12, 1),
              "frac_of_sustained": round(value / world * FLOP_PER_ITEM / 1e12 / peaks["bf16_sustained"], 4),
