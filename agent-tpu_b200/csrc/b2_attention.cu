@@ -476,6 +476,267 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
   }
 }
 
+// ---- persistent variant for S = 256 .. 512 (several key blocks per query block) ------------------
+// Same ring as attention_persist_kernel, but a ring step is one (sequence, head, query block, key
+// block): Q is re-fetched with every key block (an L2 hit; it lets P overlay the Q|K tiles exactly as
+// in the one-block kernel), and the softmax threads carry the running maximum, denominator and the
+// f32 output row across the key blocks of a query block (online softmax), writing the row once.
+struct AttStep {
+  int item, kb, nkb, b, h, qb, len, row0;
+  bool valid;
+};
+
+__device__ __forceinline__ void att_step_next(AttStep& it, const int32_t* __restrict__ lens,
+                                              const int32_t* __restrict__ cu, int S, int heads, int qblocks,
+                                              int n_items) {
+  if (++it.kb < it.nkb) return;
+  for (;;) {
+    it.item += gridDim.x;
+    if (it.item >= n_items) { it.valid = false; return; }
+    int t = it.item;
+    it.qb = t % qblocks; t /= qblocks;
+    it.h = t % heads;
+    it.b = t / heads;
+    int len = lens[it.b];
+    len = len < 0 ? 0 : (len > S ? S : len);
+    if (it.qb * QB >= len) continue;  // query block of pad rows only
+    it.len = len;
+    it.nkb = (len + KB - 1) / KB;
+    it.kb = 0;
+    it.row0 = cu ? cu[it.b] : it.b * S;
+    return;
+  }
+}
+
+__device__ __forceinline__ void att_step_init(AttStep& it, const int32_t* __restrict__ lens,
+                                              const int32_t* __restrict__ cu, int S, int heads, int qblocks,
+                                              int n_items) {
+  it.item = static_cast<int>(blockIdx.x) - static_cast<int>(gridDim.x);
+  it.kb = 0; it.nkb = 0; it.valid = true;
+  att_step_next(it, lens, cu, S, heads, qblocks, n_items);
+}
+
+__global__ void __launch_bounds__(ATT_THREADS, 2)
+attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
+                        const int32_t* __restrict__ lens, int S, int hidden, int heads, int qblocks,
+                        int n_items, const int32_t* __restrict__ cu) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bars = base + 2 * STAGE_BYTES_P;
+  auto bar = [&](int which, int s) { return bars + 8u * (which * 2 + s); };
+  enum { QKV_FULL = 0, S_FULL = 1, P_FULL = 2, O_FULL = 3, FREE = 4 };
+  const uint32_t tmem_slot = bars + 8u * 10;
+  uint8_t* smem_aligned = smem_raw + (base - raw);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 128) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar(QKV_FULL, s), 1);
+      mbar_init(bar(S_FULL, s), 1);
+      mbar_init(bar(P_FULL, s), 128);
+      mbar_init(bar(O_FULL, s), 1);
+      mbar_init(bar(FREE, s), 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 4) tmem_alloc<256>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      auto kbox_of = [&](const AttStep& it) { return (min(KB, it.len - it.kb * KB) + 31) >> 5; };
+      auto load_step = [&](const AttStep& it, int i) {
+        const int qbox = (min(QB, it.len - it.qb * QB) + 31) >> 5;
+        const int kbox = kbox_of(it);
+        const int s = i & 1;
+        const uint32_t st = base + s * STAGE_BYTES_P;
+        mbar_expect_tx(bar(QKV_FULL, s), (qbox + 2 * kbox) * 32 * 128);
+        tma_load_2d(st, &maps.m[qbox - 1], bar(QKV_FULL, s), it.h * HD, it.row0 + it.qb * QB);
+        tma_load_2d(st + TILE_BYTES, &maps.m[kbox - 1], bar(QKV_FULL, s), hidden + it.h * HD,
+                    it.row0 + it.kb * KB);
+        tma_load_2d(st + 2 * TILE_BYTES, &maps.m[kbox - 1], bar(QKV_FULL, s), 2 * hidden + it.h * HD,
+                    it.row0 + it.kb * KB);
+      };
+      auto issue_s = [&](const AttStep& it, int i) {
+        const int s = i & 1;
+        const uint32_t st = base + s * STAGE_BYTES_P;
+        mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
+        tc_fence_after();
+        const uint32_t idesc_s = umma_idesc_bf16(128, kbox_of(it) * 32, 0, 0);
+        const uint64_t qd = umma_desc_sw128(st, 16, 1024);
+        const uint64_t kd = umma_desc_sw128(st + TILE_BYTES, 16, 1024);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16(tmem_base + s * 128, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
+        umma_commit(bar(S_FULL, s));
+      };
+      AttStep ld, si, pv;
+      att_step_init(ld, lens, cu, S, heads, qblocks, n_items);
+      si = ld; pv = ld;
+      if (ld.valid) { load_step(ld, 0); att_step_next(ld, lens, cu, S, heads, qblocks, n_items); }
+      if (ld.valid) { load_step(ld, 1); att_step_next(ld, lens, cu, S, heads, qblocks, n_items); }
+      if (si.valid) { issue_s(si, 0); att_step_next(si, lens, cu, S, heads, qblocks, n_items); }
+      for (int i = 0; pv.valid; ++i) {
+        const int s = i & 1;
+        const uint32_t ph = (i >> 1) & 1;
+        const uint32_t st = base + s * STAGE_BYTES_P;
+        const int nk = kbox_of(pv) * 32;
+        mbar_wait(bar(P_FULL, s), ph);
+        tc_fence_after();
+        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
+        for (int k = 0; k < nk / 16; ++k) {
+          const uint64_t pd = umma_desc_sw128(st + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
+          const uint64_t vd = umma_desc_sw128(st + 2 * TILE_BYTES + k * 2048, 8192, 1024);
+          umma_bf16(tmem_base + s * 128, pd, vd, idesc_o, k != 0);
+        }
+        umma_commit(bar(O_FULL, s));
+        if (si.valid) { issue_s(si, i + 1); att_step_next(si, lens, cu, S, heads, qblocks, n_items); }
+        if (ld.valid) {
+          mbar_wait(bar(FREE, s), ph);
+          load_step(ld, i + 2);
+          att_step_next(ld, lens, cu, S, heads, qblocks, n_items);
+        }
+        att_step_next(pv, lens, cu, S, heads, qblocks, n_items);
+      }
+    }
+  } else {
+    const int r = threadIdx.x;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
+    float m_run = -INFINITY, l_run = 0.f;
+    float o[HD];
+    AttStep it;
+    att_step_init(it, lens, cu, S, heads, qblocks, n_items);
+    for (int i = 0; it.valid; ++i) {
+      const int s = i & 1;
+      const uint32_t ph = (i >> 1) & 1;
+      if (it.kb == 0) {
+        m_run = -INFINITY; l_run = 0.f;
+#pragma unroll
+        for (int e = 0; e < HD; ++e) o[e] = 0.f;
+      }
+      const int kvalid = min(KB, it.len - it.kb * KB);
+      const uint32_t tS = tmem_base + s * 128 + lane_base;
+      mbar_wait(bar(S_FULL, s), ph);
+      tc_fence_after();
+      float mx = -INFINITY;
+      for (int c = 0; c < 4; ++c) {
+        if (c * 32 < kvalid) {
+          uint32_t v[32];
+          tmem_ld_32x32(tS + c * 32, v);
+          tmem_ld_wait();
+          if (c * 32 + 32 <= kvalid) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2)
+              mx = fmaxf(mx, fmaxf(__uint_as_float(v[j]), __uint_as_float(v[j + 1])));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (c * 32 + j < kvalid) mx = fmaxf(mx, __uint_as_float(v[j]));
+          }
+        }
+      }
+      const float m_new = fmaxf(m_run, mx);
+      const float alpha = ex2_approx((m_run - m_new) * sl2);
+      const float moff = m_new * sl2;
+      const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
+      uint64_t sum2 = f32x2(0.f, 0.f);
+      float rowsum = 0.f;
+      for (int c = 0; c < 4; ++c) {
+        if (c * 32 < kvalid) {
+          uint32_t packed[16];
+          uint32_t v[32];
+          tmem_ld_32x32(tS + c * 32, v);
+          tmem_ld_wait();
+          if (c * 32 + 32 <= kvalid) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              float p0, p1;
+              f32x2_split(ffma2(f32x2_bits(v[j], v[j + 1]), scale2, shift2), p0, p1);
+              p0 = ex2_approx(p0);
+              p1 = ex2_approx(p1);
+              sum2 = fadd2(sum2, f32x2(p0, p1));
+              packed[j >> 1] = pack_bf16x2(p0, p1);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float p0 = (c * 32 + j < kvalid) ? ex2_approx(fmaf(__uint_as_float(v[j]), sl2, -moff)) : 0.f;
+              const float p1 = (c * 32 + j + 1 < kvalid) ? ex2_approx(fmaf(__uint_as_float(v[j + 1]), sl2, -moff)) : 0.f;
+              rowsum += p0 + p1;
+              packed[j >> 1] = pack_bf16x2(p0, p1);
+            }
+          }
+          uint8_t* tile = smem_aligned + s * STAGE_BYTES_P + (c >> 1) * TILE_BYTES + r * 128;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
+            *reinterpret_cast<uint4*>(tile + chunk * 16) =
+                make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
+          }
+        }
+      }
+      {
+        float s0, s1;
+        f32x2_split(sum2, s0, s1);
+        rowsum += s0 + s1;
+      }
+      l_run = l_run * alpha + rowsum;
+      m_run = m_new;
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar(P_FULL, s));
+
+      mbar_wait(bar(O_FULL, s), ph);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tS + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[c * 32 + j] = fmaf(o[c * 32 + j], alpha, __uint_as_float(v[j]));
+      }
+      tc_fence_before();
+      mbar_arrive(bar(FREE, s));
+
+      if (it.kb + 1 == it.nkb) {
+        const int qvalid = min(QB, it.len - it.qb * QB);
+        if (r < qvalid) {
+          const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+          __nv_bfloat16* dst = out + static_cast<size_t>(it.row0 + it.qb * QB + r) * hidden + it.h * HD;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4 w;
+            w.x = pack_bf16x2(o[j * 8 + 0] * inv, o[j * 8 + 1] * inv);
+            w.y = pack_bf16x2(o[j * 8 + 2] * inv, o[j * 8 + 3] * inv);
+            w.z = pack_bf16x2(o[j * 8 + 4] * inv, o[j * 8 + 5] * inv);
+            w.w = pack_bf16x2(o[j * 8 + 6] * inv, o[j * 8 + 7] * inv);
+            *reinterpret_cast<uint4*>(dst + j * 8) = w;
+          }
+        }
+      }
+      att_step_next(it, lens, cu, S, heads, qblocks, n_items);
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem_base);
+  }
+}
+
 }  // namespace
 
 // `out` holds four tensor maps (box rows 32, 64, 96, 128) packed into AttentionMaps::raw.
@@ -507,6 +768,8 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
                                     ATT_SMEM_MULTI));
     B2_CUDA_OK(cudaFuncSetAttribute(attention_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     ATT_SMEM_PERSIST));
+    B2_CUDA_OK(cudaFuncSetAttribute(attention_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    ATT_SMEM_PERSIST));
     configured[dev] = true;
   }
   const int heads = hidden / HD, qblocks = S / QB;
@@ -524,6 +787,13 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
     const int ctas = items < 2 * sms ? items : 2 * sms;
     attention_persist_kernel<<<ctas, ATT_THREADS, ATT_SMEM_PERSIST, stream>>>(maps, out, lens, S, hidden,
                                                                              heads, items, cu);
+  } else if (!one_shot) {
+    int sms = 0;
+    B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int items = static_cast<int>(grid);
+    const int ctas = items < 2 * sms ? items : 2 * sms;
+    attention_stream_kernel<<<ctas, ATT_THREADS, ATT_SMEM_PERSIST, stream>>>(maps, out, lens, S, hidden, heads,
+                                                                            qblocks, items, cu);
   } else if (S == QB)
     attention_kernel<true><<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM_SINGLE, stream>>>(
         maps, out, lens, S, hidden, heads, qblocks, cu);
