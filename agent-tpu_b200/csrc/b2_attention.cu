@@ -249,6 +249,89 @@ attention_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict
   }
 }
 
+// Softmax of one 128-key block for one query row, shared by the persistent kernels.
+//   tS      TMEM address of this thread's row of S (lane bits included)
+//   kvalid  keys of this block that belong to the sequence (1..128)
+//   m_run   running row maximum from earlier key blocks (-inf for the first / only block)
+//   prow    this row's 128 bytes in the first P tile (second tile at +TILE_BYTES), 128-byte swizzled
+// Returns the new maximum and the sum of exp over this block; writes P (bf16) for every 32-key chunk
+// that holds a valid key. TMEM loads are double-buffered: chunk c+1 is in flight while chunk c is
+// reduced (tcgen05.wait::ld waits for everything issued, so the next load is issued right after it).
+// A chunk that lies wholly inside the sequence takes the unmasked path: FMNMX3, packed FFMA2 / FADD2,
+// two MUFU.EX2 and one bf16x2 convert per key pair; only the chunk that straddles `kvalid` is masked.
+__device__ __forceinline__ void softmax_block(uint32_t tS, int kvalid, float sl2, float m_run, uint8_t* prow,
+                                              int r, float& m_new, float& rowsum) {
+  const int nch = (kvalid + 31) >> 5;
+  uint32_t va[32], vb[32];
+  float mx = -INFINITY;
+  tmem_ld_32x32(tS, va);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    if (c < nch) {
+      uint32_t(&cur)[32] = (c & 1) ? vb : va;
+      uint32_t(&nxt)[32] = (c & 1) ? va : vb;
+      tmem_ld_wait();
+      if (c + 1 < nch) tmem_ld_32x32(tS + (c + 1) * 32, nxt);
+      if (c * 32 + 32 <= kvalid) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 2)
+          mx = fmaxf(mx, fmaxf(__uint_as_float(cur[j]), __uint_as_float(cur[j + 1])));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (c * 32 + j < kvalid) mx = fmaxf(mx, __uint_as_float(cur[j]));
+      }
+    }
+  }
+  m_new = fmaxf(m_run, mx);
+  const float moff = m_new * sl2;
+  const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
+  uint64_t sum2 = f32x2(0.f, 0.f);
+  float sum1 = 0.f;
+  tmem_ld_32x32(tS, va);  // second pass, chunk 0 (the one TMEM latency per block that stays exposed)
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    if (c < nch) {
+      uint32_t(&cur)[32] = (c & 1) ? vb : va;
+      uint32_t(&nxt)[32] = (c & 1) ? va : vb;
+      uint32_t packed[16];
+      tmem_ld_wait();
+      if (c + 1 < nch) tmem_ld_32x32(tS + (c + 1) * 32, nxt);
+      if (c * 32 + 32 <= kvalid) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          float p0, p1;
+          f32x2_split(ffma2(f32x2_bits(cur[j], cur[j + 1]), scale2, shift2), p0, p1);
+          p0 = ex2_approx(p0);
+          p1 = ex2_approx(p1);
+          sum2 = fadd2(sum2, f32x2(p0, p1));
+          packed[j >> 1] = pack_bf16x2(p0, p1);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float p0 = (c * 32 + j < kvalid) ? ex2_approx(fmaf(__uint_as_float(cur[j]), sl2, -moff)) : 0.f;
+          const float p1 =
+              (c * 32 + j + 1 < kvalid) ? ex2_approx(fmaf(__uint_as_float(cur[j + 1]), sl2, -moff)) : 0.f;
+          sum1 += p0 + p1;
+          packed[j >> 1] = pack_bf16x2(p0, p1);
+        }
+      }
+      // keys [c*32, c*32+32) -> tile (c >> 1), 16-byte chunks ((c & 1) * 4 + j) ^ (r & 7)
+      uint8_t* tile = prow + (c >> 1) * TILE_BYTES;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
+        *reinterpret_cast<uint4*>(tile + chunk * 16) =
+            make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
+      }
+    }
+  }
+  float s0, s1;
+  f32x2_split(sum2, s0, s1);
+  rowsum = sum1 + s0 + s1;
+}
+
 // ---- persistent, software-pipelined variant for S = 128 (one key block per sequence) -------------
 // Two CTAs per SM, each walking (sequence, head) items i = blockIdx.x, + gridDim.x, ... with two
 // stages of {Q, K, V} tiles in shared memory and two S/O accumulators in TMEM:
@@ -373,69 +456,8 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       const uint32_t tS = tmem_base + s * 128 + lane_base;
       mbar_wait(bar(S_FULL, s), ph);
       tc_fence_after();
-      // A chunk of 32 keys that lies wholly inside the sequence takes the unmasked path: three-input
-      // max (FMNMX3), packed FFMA2 / FADD2, two MUFU.EX2 and one bf16x2 convert per key pair. Only the
-      // one chunk that straddles `len` pays for per-key masking.
-      float mx = -INFINITY;
-      for (int c = 0; c < 4; ++c) {
-        if (c * 32 < len) {
-          uint32_t v[32];
-          tmem_ld_32x32(tS + c * 32, v);
-          tmem_ld_wait();
-          if (c * 32 + 32 <= len) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2)
-              mx = fmaxf(mx, fmaxf(__uint_as_float(v[j]), __uint_as_float(v[j + 1])));
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (c * 32 + j < len) mx = fmaxf(mx, __uint_as_float(v[j]));
-          }
-        }
-      }
-      const float moff = mx * sl2;
-      const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
-      uint64_t sum2 = f32x2(0.f, 0.f);
-      float rowsum = 0.f;
-      for (int c = 0; c < 4; ++c) {
-        if (c * 32 < len) {
-          uint32_t packed[16];
-          uint32_t v[32];
-          tmem_ld_32x32(tS + c * 32, v);
-          tmem_ld_wait();
-          if (c * 32 + 32 <= len) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              float p0, p1;
-              f32x2_split(ffma2(f32x2_bits(v[j], v[j + 1]), scale2, shift2), p0, p1);
-              p0 = ex2_approx(p0);
-              p1 = ex2_approx(p1);
-              sum2 = fadd2(sum2, f32x2(p0, p1));
-              packed[j >> 1] = pack_bf16x2(p0, p1);
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              const float p0 = (c * 32 + j < len) ? ex2_approx(fmaf(__uint_as_float(v[j]), sl2, -moff)) : 0.f;
-              const float p1 = (c * 32 + j + 1 < len) ? ex2_approx(fmaf(__uint_as_float(v[j + 1]), sl2, -moff)) : 0.f;
-              rowsum += p0 + p1;
-              packed[j >> 1] = pack_bf16x2(p0, p1);
-            }
-          }
-          uint8_t* tile = smem_aligned + s * STAGE_BYTES_P + (c >> 1) * TILE_BYTES + r * 128;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
-            *reinterpret_cast<uint4*>(tile + chunk * 16) =
-                make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
-          }
-        }
-      }
-      {
-        float s0, s1;
-        f32x2_split(sum2, s0, s1);
-        rowsum += s0 + s1;
-      }
+      float m_new, rowsum;
+      softmax_block(tS, len, sl2, -INFINITY, smem_aligned + s * STAGE_BYTES_P + r * 128, r, m_new, rowsum);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(bar(P_FULL, s));
@@ -627,68 +649,9 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
       const uint32_t tS = tmem_base + s * 128 + lane_base;
       mbar_wait(bar(S_FULL, s), ph);
       tc_fence_after();
-      float mx = -INFINITY;
-      for (int c = 0; c < 4; ++c) {
-        if (c * 32 < kvalid) {
-          uint32_t v[32];
-          tmem_ld_32x32(tS + c * 32, v);
-          tmem_ld_wait();
-          if (c * 32 + 32 <= kvalid) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2)
-              mx = fmaxf(mx, fmaxf(__uint_as_float(v[j]), __uint_as_float(v[j + 1])));
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (c * 32 + j < kvalid) mx = fmaxf(mx, __uint_as_float(v[j]));
-          }
-        }
-      }
-      const float m_new = fmaxf(m_run, mx);
+      float m_new, rowsum;
+      softmax_block(tS, kvalid, sl2, m_run, smem_aligned + s * STAGE_BYTES_P + r * 128, r, m_new, rowsum);
       const float alpha = ex2_approx((m_run - m_new) * sl2);
-      const float moff = m_new * sl2;
-      const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
-      uint64_t sum2 = f32x2(0.f, 0.f);
-      float rowsum = 0.f;
-      for (int c = 0; c < 4; ++c) {
-        if (c * 32 < kvalid) {
-          uint32_t packed[16];
-          uint32_t v[32];
-          tmem_ld_32x32(tS + c * 32, v);
-          tmem_ld_wait();
-          if (c * 32 + 32 <= kvalid) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              float p0, p1;
-              f32x2_split(ffma2(f32x2_bits(v[j], v[j + 1]), scale2, shift2), p0, p1);
-              p0 = ex2_approx(p0);
-              p1 = ex2_approx(p1);
-              sum2 = fadd2(sum2, f32x2(p0, p1));
-              packed[j >> 1] = pack_bf16x2(p0, p1);
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              const float p0 = (c * 32 + j < kvalid) ? ex2_approx(fmaf(__uint_as_float(v[j]), sl2, -moff)) : 0.f;
-              const float p1 = (c * 32 + j + 1 < kvalid) ? ex2_approx(fmaf(__uint_as_float(v[j + 1]), sl2, -moff)) : 0.f;
-              rowsum += p0 + p1;
-              packed[j >> 1] = pack_bf16x2(p0, p1);
-            }
-          }
-          uint8_t* tile = smem_aligned + s * STAGE_BYTES_P + (c >> 1) * TILE_BYTES + r * 128;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
-            *reinterpret_cast<uint4*>(tile + chunk * 16) =
-                make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
-          }
-        }
-      }
-      {
-        float s0, s1;
-        f32x2_split(sum2, s0, s1);
-        rowsum += s0 + s1;
-      }
       l_run = l_run * alpha + rowsum;
       m_run = m_new;
       fence_proxy_async_smem();
