@@ -36,6 +36,8 @@ constexpr uint32_t TILE_BYTES = 128 * 64 * 2;  // 16 KiB: a [128 x 64] bf16 tile
 constexpr uint32_t ATT_SMEM_SINGLE = 1024 + 3 * TILE_BYTES + 64;
 constexpr uint32_t ATT_SMEM_MULTI = 1024 + 5 * TILE_BYTES + 64;
 
+unsigned long long* g_att_trace = nullptr;
+
 struct AttMaps {
   CUtensorMap m[4];  // box rows 32, 64, 96, 128 over the same [rows, 3H] buffer
 };
@@ -343,12 +345,23 @@ __device__ __forceinline__ void softmax_block(uint32_t tS, int kvalid, float sl2
 // Per-item set-up (TMEM allocation, barrier initialisation, CTA launch) is paid once per CTA
 // instead of 12,288 times per layer.
 constexpr uint32_t STAGE_BYTES_P = 3 * TILE_BYTES;
-constexpr uint32_t ATT_SMEM_PERSIST = 1024 + 2 * STAGE_BYTES_P + 128;
+constexpr int PERSIST_MAX_ITEMS = 256;  // (sequence, head) items one CTA may walk; the launcher sizes the grid
+constexpr uint32_t ATT_SMEM_PERSIST = 1024 + 2 * STAGE_BYTES_P + 128 + PERSIST_MAX_ITEMS * 8;
 
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
                          const int32_t* __restrict__ lens, int S, int hidden, int heads, int n_items,
-                         const int32_t* __restrict__ cu) {
+                         const int32_t* __restrict__ cu, unsigned long long* __restrict__ trace) {
+  // developer timeline (dev_check "atttrace"): CTA 0 records %globaltimer at each pipeline event of
+  // its first 64 items: [item][0..3] control thread (P seen, PV committed, O seen, load issued),
+  // [item][4..7] softmax row 0 (S seen, P arrived, O seen, row stored)
+  auto stamp = [&](int item, int slot) {
+    if (trace && blockIdx.x == 0 && item < 64) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      trace[item * 8 + slot] = t;
+    }
+  };
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -365,6 +378,17 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
   const int lane = threadIdx.x & 31;
   const int my_items = (n_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                        static_cast<int>(gridDim.x);
+  // Per-item (length, first row) looked up ONCE into shared memory: the control thread's loop is a
+  // chain of dependent steps, and a global load of lens[] / cu[] in it costs ~0.5 us each time
+  // (measured with the dev_check timeline: 2 us of a 4.8 us item were such loads).
+  int2* meta = reinterpret_cast<int2*>(smem_aligned + 2 * STAGE_BYTES_P + 128);
+  for (int i = threadIdx.x; i < my_items; i += blockDim.x) {
+    const int idx = blockIdx.x + i * gridDim.x;
+    const int b = idx / heads;
+    int len = lens[b];
+    len = len < 1 ? 1 : (len > S ? S : len);
+    meta[i] = make_int2(len, cu ? cu[b] : b * S);
+  }
 
   if (threadIdx.x == 128) {
     for (int s = 0; s < 2; ++s) {
@@ -386,11 +410,10 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
     if (lane == 0) {
       auto load_item = [&](int i) {
         const int idx = blockIdx.x + i * gridDim.x;
-        const int b = idx / heads, h = idx - b * heads;
-        int len = lens[b];
-        len = len < 1 ? 1 : (len > S ? S : len);
-        const int row0 = cu ? cu[b] : b * S;
-        const int box = (len + 31) >> 5;
+        const int h = idx % heads;
+        const int2 md = meta[i];
+        const int row0 = md.y;
+        const int box = (md.x + 31) >> 5;
         const int s = i & 1;
         const uint32_t st = base + s * STAGE_BYTES_P;
         mbar_expect_tx(bar(QKV_FULL, s), 3 * box * 32 * 128);
@@ -398,12 +421,18 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
         tma_load_2d(st + TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), hidden + h * HD, row0);
         tma_load_2d(st + 2 * TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), 2 * hidden + h * HD, row0);
       };
-      auto nk_of = [&](int i) {
+      // pull item i's tiles from DRAM into L2 ahead of its TMA load (no shared memory needed)
+      auto prefetch_item = [&](int i) {
         const int idx = blockIdx.x + i * gridDim.x;
-        int len = lens[idx / heads];
-        len = len < 1 ? 1 : (len > S ? S : len);
-        return ((len + 31) >> 5) * 32;
+        const int h = idx % heads;
+        const int2 md = meta[i];
+        const int row0 = md.y;
+        const int box = (md.x + 31) >> 5;
+        tma_prefetch_2d(&maps.m[box - 1], h * HD, row0);
+        tma_prefetch_2d(&maps.m[box - 1], hidden + h * HD, row0);
+        tma_prefetch_2d(&maps.m[box - 1], 2 * hidden + h * HD, row0);
       };
+      auto nk_of = [&](int i) { return ((meta[i].x + 31) >> 5) * 32; };
       auto issue_s = [&](int i) {
         const int s = i & 1;
         const uint32_t st = base + s * STAGE_BYTES_P;
@@ -419,6 +448,8 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       };
       if (my_items > 0) load_item(0);
       if (my_items > 1) load_item(1);
+      if (my_items > 2) prefetch_item(2);
+      if (my_items > 3) prefetch_item(3);
       if (my_items > 0) issue_s(0);
       for (int i = 0; i < my_items; ++i) {
         const int s = i & 1;
@@ -426,6 +457,7 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
         const uint32_t st = base + s * STAGE_BYTES_P;
         const int nk = nk_of(i);
         mbar_wait(bar(P_FULL, s), ph);
+        stamp(i, 0);
         tc_fence_after();
         constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
         for (int k = 0; k < nk / 16; ++k) {
@@ -435,9 +467,16 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
         }
         umma_commit(bar(O_FULL, s));
         if (i + 1 < my_items) issue_s(i + 1);  // right behind P·V: the softmax warps find S ready
+        stamp(i, 1);
         if (i + 2 < my_items) {
-          mbar_wait(bar(FREE, s), ph);  // O_i has been read: stage s (smem and TMEM) is free again
+          // stage s's shared memory is free as soon as P·V(i) has completed; its TMEM columns are
+          // only needed again by S(i+2), which is issued one iteration later, after the softmax
+          // threads have read O(i) (they arrive on P_FULL(i+1) only after that read)
+          mbar_wait(bar(O_FULL, s), ph);
+          stamp(i, 2);
           load_item(i + 2);
+          if (i + 4 < my_items) prefetch_item(i + 4);
+          stamp(i, 3);
         }
       }
     }
@@ -449,23 +488,25 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       const int s = i & 1;
       const uint32_t ph = (i >> 1) & 1;
       const int idx = blockIdx.x + i * gridDim.x;
-      const int b = idx / heads, h = idx - b * heads;
-      int len = lens[b];
-      len = len < 1 ? 1 : (len > S ? S : len);
-      const int row0 = cu ? cu[b] : b * S;
+      const int h = idx % heads;
+      const int2 md = meta[i];
+      const int len = md.x, row0 = md.y;
       const uint32_t tS = tmem_base + s * 128 + lane_base;
       mbar_wait(bar(S_FULL, s), ph);
+      if (r == 0) stamp(i, 4);
       tc_fence_after();
       float m_new, rowsum;
       softmax_block(tS, len, sl2, -INFINITY, smem_aligned + s * STAGE_BYTES_P + r * 128, r, m_new, rowsum);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(bar(P_FULL, s));
+      if (r == 0) stamp(i, 5);
 
       const float inv = rowsum > 0.f ? 1.0f / rowsum : 0.f;
       __nv_bfloat16* dst = out + static_cast<size_t>(row0 + r) * hidden + h * HD;
       const bool store = r < len;
       mbar_wait(bar(O_FULL, s), ph);
+      if (r == 0) stamp(i, 6);
       tc_fence_after();
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -486,6 +527,7 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       }
       tc_fence_before();
       mbar_arrive(bar(FREE, s));
+      if (r == 0) stamp(i, 7);
     }
   }
 
@@ -702,6 +744,9 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
 
 }  // namespace
 
+// developer hook (dev_check): device buffer of 64 x 8 u64 that CTA 0 of the S=128 kernel fills
+void attention_set_trace(unsigned long long* dev_buf) { g_att_trace = dev_buf; }
+
 // `out` holds four tensor maps (box rows 32, 64, 96, 128) packed into AttentionMaps::raw.
 int attention_tmaps(AttentionMaps* out, const void* qkv, int rows, int hidden) {
   static_assert(sizeof(AttentionMaps) == sizeof(AttMaps), "AttentionMaps layout");
@@ -747,9 +792,11 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
     int sms = 0;
     B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int items = B * heads;
-    const int ctas = items < 2 * sms ? items : 2 * sms;
+    int ctas = items < 2 * sms ? items : 2 * sms;
+    const int need = (items + PERSIST_MAX_ITEMS - 1) / PERSIST_MAX_ITEMS;  // keep a CTA's item list in smem
+    if (ctas < need) ctas = need;
     attention_persist_kernel<<<ctas, ATT_THREADS, ATT_SMEM_PERSIST, stream>>>(maps, out, lens, S, hidden,
-                                                                             heads, items, cu);
+                                                                             heads, items, cu, g_att_trace);
   } else if (!one_shot) {
     int sms = 0;
     B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

@@ -94,6 +94,13 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
       ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// 2-D tiled prefetch global -> L2 (no shared memory, no completion signal): used to pull tiles that
+// will be TMA-loaded a few pipeline steps later out of DRAM ahead of time.
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* tmap, int32_t c0, int32_t c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1)
+               : "memory");
+}
 // 2-D tiled store shared -> global (bulk async group).
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tmap, uint32_t src_smem,
                                              int32_t c0, int32_t c1) {

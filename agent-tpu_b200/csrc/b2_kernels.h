@@ -61,6 +61,8 @@ int attention_tmaps(AttentionMaps* out, const void* qkv, int rows, int hidden);
 int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16* out,
                    const int32_t* lens, int B, int S, int hidden, const int32_t* cu = nullptr);
 
+void attention_set_trace(unsigned long long* dev_buf);  // developer timeline hook (dev_check)
+
 // ---- element-wise / row kernels (b2_rows.cu) ---------------------------------------------------
 // out[row] = LayerNorm(word[ids[row]] + pos[row % S] + type[0]) * gamma + beta  -> bf16
 // packed: with lens / cu given, token (b, s) is written to row cu[b] + s and pad positions are skipped.

@@ -340,6 +340,22 @@ int main(int argc, char** argv) {
     fails += check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, true);
     fails += check_attention(256, 512, 768, {512, 300}, true);
   }
+  if (!strcmp(what, "atttrace")) {
+    unsigned long long* dtr; CK(cudaMalloc(&dtr, 64 * 8 * 8)); CK(cudaMemset(dtr, 0, 64 * 8 * 8));
+    check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, false);   // warm
+    attention_set_trace(dtr);
+    check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, false);
+    attention_set_trace(nullptr);
+    std::vector<unsigned long long> tr(64 * 8);
+    CK(cudaMemcpy(tr.data(), dtr, tr.size() * 8, cudaMemcpyDeviceToHost));
+    unsigned long long t0 = tr[4];
+    printf("item: ctl[Pseen PVcommit Oseen loaded] sm[Sseen Parrive Oseen stored]  (ns since first S seen)\n");
+    for (int i = 0; i < 40; ++i) {
+      printf("%2d:", i);
+      for (int k = 0; k < 8; ++k) printf(" %7lld", tr[i * 8 + k] ? (long long)(tr[i * 8 + k] - t0) : -1ll);
+      printf("\n");
+    }
+  }
   if (!strcmp(what, "all") || !strcmp(what, "rows")) {
     fails += check_rows(1000, 128, 128, 500, false);
     fails += check_rows(131072, 128, 768, 30522, true);
