@@ -1,21 +1,33 @@
 // b2_attention.cu — masked self-attention for the encoder, head dim 64, on tcgen05 + TMA.
 //
-// One CTA handles one (sequence, head, 128-query block). For each 128-key block it runs
+// Persistent kernels, two CTAs per SM. A CTA walks its work items through a two-stage ring of
+// {Q, K, V} tiles in shared memory and two S/O accumulators in TMEM:
 //   S = Q·Kᵀ            tcgen05.mma 128 x n x 64  (Q, K: K-major 128-byte-swizzled TMA tiles)
-//   P = exp2((S-m)·c)    one thread per query row, S read from TMEM, keys >= len masked out
-//   O_blk = P·V          tcgen05.mma 128 x 64 x n  (P: written to swizzled smem as the A operand,
-//                                                  V: MN-major TMA tile, no transpose needed)
+//   P = exp2((S-m)·c)    two threads per query row read S from TMEM; keys >= len are masked out
+//   O = P·V              tcgen05.mma 128 x 64 x n  (P: written bf16 into the swizzled smem of the dead
+//                                                  Q|K tiles as the A operand; V: MN-major TMA tile,
+//                                                  no transpose; O accumulates over S's TMEM columns)
 // with n = the block's valid keys rounded up to 32: the TMA boxes (four tensor maps with 32, 64, 96
-// and 128 rows), the UMMA N of Q·Kᵀ and the K extent of P·V all shrink with the sequence, so a
-// 40-token sentence moves and multiplies a third of what a 128-token one does. Rows of the tiles
-// beyond the box hold stale shared memory; they are never read by an MMA whose result is kept.
+// and 128 rows), the UMMA N of Q·Kᵀ and the K extent of P·V all shrink with the sequence. Rows of
+// the tiles beyond the box hold stale shared memory; no MMA whose result is kept reads them.
 //
-// Two instantiations:
-//   SINGLE (S <= 128): one key block. P overlays the Q|K tiles (dead once Q·Kᵀ has completed) and
-//     O overlays S in TMEM, so a CTA needs 48 KiB of smem and 128 TMEM columns: 4 CTAs per SM
-//     overlap each other's load -> MMA -> softmax -> MMA -> store chains.
-//   MULTI (S = 256..512): online softmax over key blocks, running f32 output in registers; key
-//     blocks and query blocks wholly beyond the sequence's length are skipped.
+//   control thread : item i+1's Q·Kᵀ is issued right behind item i's P·V and item i+2's loads go out
+//                    as soon as P·V(i) has completed (tiles two further ahead are prefetched into L2),
+//                    so the tensor core never waits for a load and the softmax warps never wait for
+//                    Q·Kᵀ. Per-item (length, first row) are looked up once into shared memory: a
+//                    global load in this thread's dependent chain costs ~0.5 us each time.
+//   softmax warps  : eight per CTA, two threads per query row (keys 0-63 / 64-127, then output columns
+//                    0-31 / 32-63); the row maximum and denominator are exchanged through shared
+//                    memory. This part is a chain of TMEM loads, MUFU.EX2 and row-strided stores: it
+//                    needs warps, not width, to hide its latency (measured with the timeline below:
+//                    2.0 us softmax + 1.0 us store per 128-key item with one thread per row).
+//
+// attention_persist_kernel  S = 128: one item = (sequence, head), one key block.
+// attention_stream_kernel   S = 256..512: one ring step = (sequence, head, query block, key block);
+//                           Q is re-fetched with every key block (an L2 hit; it lets P overlay the
+//                           Q|K tiles exactly as in the one-block kernel) and the softmax threads carry
+//                           the running maximum, denominator and f32 output row across the key blocks
+//                           (online softmax); blocks wholly beyond the sequence are skipped.
 //
 // No reference counterpart: the reference's model is an opaque TFLite graph
 // (ops/map_classify_tpu.py:71-72). Semantics follow BertSelfAttention (scores/sqrt(d) + additive
@@ -28,13 +40,18 @@ namespace b2 {
 
 namespace {
 
-constexpr int ATT_THREADS = 160;  // warps 0-3: one query row per thread; warp 4: TMA + MMA issue
-constexpr int QB = 128;           // queries per CTA
-constexpr int KB = 128;           // keys per block
-constexpr int HD = 64;            // head dim
+constexpr int ATT_THREADS = 288;  // warps 0-7: softmax (2 threads per query row); warp 8: TMA + MMA issue
+constexpr int ATT_SOFTMAX_THREADS = 256;
+constexpr int QB = 128;  // queries per item / step
+constexpr int KB = 128;  // keys per block
+constexpr int HD = 64;   // head dim
 constexpr uint32_t TILE_BYTES = 128 * 64 * 2;  // 16 KiB: a [128 x 64] bf16 tile
-constexpr uint32_t ATT_SMEM_SINGLE = 1024 + 3 * TILE_BYTES + 64;
-constexpr uint32_t ATT_SMEM_MULTI = 1024 + 5 * TILE_BYTES + 64;
+constexpr uint32_t STAGE_BYTES = 3 * TILE_BYTES;
+constexpr int PERSIST_MAX_ITEMS = 256;  // items one CTA of the S=128 kernel may walk (grid is sized for it)
+constexpr uint32_t OFF_BARS = 2 * STAGE_BYTES;
+constexpr uint32_t OFF_RED = OFF_BARS + 128;          // float[4][128]: max[2][128], sum[2][128]
+constexpr uint32_t OFF_META = OFF_RED + 4 * 128 * 4;  // int2[PERSIST_MAX_ITEMS]
+constexpr uint32_t ATT_SMEM = 1024 + OFF_META + PERSIST_MAX_ITEMS * 8;
 
 unsigned long long* g_att_trace = nullptr;
 
@@ -42,319 +59,102 @@ struct AttMaps {
   CUtensorMap m[4];  // box rows 32, 64, 96, 128 over the same [rows, 3H] buffer
 };
 
-template <bool SINGLE>
-__global__ void __launch_bounds__(ATT_THREADS, SINGLE ? 4 : 2)
-attention_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
-                 const int32_t* __restrict__ lens, int S, int hidden, int heads, int qblocks,
-                 const int32_t* __restrict__ cu) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t sQ = base;
-  const uint32_t sK = base + TILE_BYTES;
-  const uint32_t sV = base + 2 * TILE_BYTES;
-  // P: two [128 x 64] K-major tiles (keys 0-63, 64-127)
-  constexpr uint32_t P_OFF = SINGLE ? 0u : 3 * TILE_BYTES;
-  const uint32_t sP = base + P_OFF;
-  const uint32_t bars = base + (SINGLE ? 3 : 5) * TILE_BYTES;
-  const uint32_t q_full = bars, kv_full = bars + 8, s_full = bars + 16, p_full = bars + 24,
-                 o_full = bars + 32, tmem_slot = bars + 40;
-  uint8_t* smem_aligned = smem_raw + (base - raw);
-  volatile uint32_t* tmem_slot_ptr =
-      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+enum { QKV_FULL = 0, S_FULL = 1, P_FULL = 2, O_FULL = 3, FREE = 4 };
 
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
+__device__ __forceinline__ void softmax_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-  int cta = blockIdx.x;
-  const int qb = cta % qblocks; cta /= qblocks;
-  const int h = cta % heads;
-  const int b = cta / heads;
-  int len = lens[b];
-  len = len < 0 ? 0 : (len > S ? S : len);
-  const int nkb = (len + KB - 1) / KB;
-  const int row0 = cu ? cu[b] : b * S;  // first token row of this sequence (packed or padded)
-  if (qb * QB >= len) return;           // query block of pad rows only: nothing to compute or store
-  const int qvalid = min(QB, len - qb * QB);
-  constexpr uint32_t TMEM_COLS = SINGLE ? 128 : 256;
-
-  if (threadIdx.x == 128) {
-    mbar_init(q_full, 1);
-    mbar_init(kv_full, 1);
-    mbar_init(s_full, 1);
-    mbar_init(p_full, 128);
-    mbar_init(o_full, 1);
-    fence_barrier_init();
-  }
-  if (warp == 4) tmem_alloc<TMEM_COLS>(tmem_slot);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot_ptr;
-  const uint32_t tmem_S = tmem_base;                         // up to 128 columns
-  const uint32_t tmem_O = tmem_base + (SINGLE ? 0u : 128u);  // 64 columns (SINGLE: over S)
-
-  if (warp == 4) {
-    if (lane == 0) {
-      const int qbox = (qvalid + 31) >> 5;  // 1..4 -> 32..128 rows
-      mbar_expect_tx(q_full, qbox * 32 * 128);
-      tma_load_2d(sQ, &maps.m[qbox - 1], q_full, h * HD, row0 + qb * QB);
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int kvalid = min(KB, len - kb * KB);
-        const int kbox = (kvalid + 31) >> 5;
-        const int nk = kbox * 32;  // keys this block's MMAs cover
-        if (kb > 0) mbar_wait(o_full, (kb - 1) & 1);  // P·V of the previous block has read K/V/P
-        mbar_expect_tx(kv_full, 2 * nk * 128);
-        tma_load_2d(sK, &maps.m[kbox - 1], kv_full, hidden + h * HD, row0 + kb * KB);
-        tma_load_2d(sV, &maps.m[kbox - 1], kv_full, 2 * hidden + h * HD, row0 + kb * KB);
-        if (kb == 0) mbar_wait(q_full, 0);
-        mbar_wait(kv_full, kb & 1);
-        tc_fence_after();
-        {
-          const uint32_t idesc_s = umma_idesc_bf16(128, nk, 0, 0);
-          const uint64_t qd = umma_desc_sw128(sQ, 16, 1024);
-          const uint64_t kd = umma_desc_sw128(sK, 16, 1024);
-#pragma unroll
-          for (int k = 0; k < HD / 16; ++k) umma_bf16(tmem_S, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
-        }
-        umma_commit(s_full);
-        mbar_wait(p_full, kb & 1);
-        tc_fence_after();
-        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
-        for (int k = 0; k < nk / 16; ++k) {
-          // A = P: K-major, 64 keys per 16 KiB tile, 32 bytes per K=16 step inside the swizzle atom
-          const uint64_t pd = umma_desc_sw128(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
-          // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes per step
-          const uint64_t vd = umma_desc_sw128(sV + k * 2048, 8192, 1024);
-          umma_bf16(tmem_O, pd, vd, idesc_o, k != 0);
-        }
-        umma_commit(o_full);
-      }
-    }
-  } else {
-    // ===== softmax / output rows: thread r owns query row r =====
-    const int r = threadIdx.x;
-    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
-    const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
-    float m_run = -INFINITY, l_run = 0.f;
-    float o[SINGLE ? 1 : HD];
-    if (!SINGLE) {
-#pragma unroll
-      for (int i = 0; i < (SINGLE ? 1 : HD); ++i) o[i] = 0.f;
-    }
-
-    for (int kb = 0; kb < nkb; ++kb) {
-      mbar_wait(s_full, kb & 1);
-      tc_fence_after();
-      const int kvalid = min(KB, len - kb * KB);
-      float mx = -INFINITY;
-      for (int c = 0; c < 4; ++c) {
-        if (c * 32 < kvalid) {
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_S + lane_base + c * 32, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c * 32 + j < kvalid) mx = fmaxf(mx, __uint_as_float(v[j]));
-        }
-      }
-      // rows of stale shared memory (beyond the Q box) may hold anything, NaN included; their
-      // results are never stored, they only must not disturb the arithmetic of this thread
-      const float m_new = fmaxf(m_run, mx);
-      const float alpha = exp2f((m_run - m_new) * sl2);
-      float rowsum = 0.f;
-      for (int c = 0; c < 4; ++c) {
-        if (c * 32 < kvalid) {  // chunks at or beyond the key box are never read by the P·V MMA
-          uint32_t packed[16];
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_S + lane_base + c * 32, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            float p0 = (c * 32 + j < kvalid) ? exp2f((__uint_as_float(v[j]) - m_new) * sl2) : 0.f;
-            float p1 = (c * 32 + j + 1 < kvalid) ? exp2f((__uint_as_float(v[j + 1]) - m_new) * sl2) : 0.f;
-            rowsum += p0 + p1;
-            packed[j >> 1] = pack_bf16x2(p0, p1);
-          }
-          // (SINGLE: P lands on the Q|K tiles; safe, s_full is only signalled once Q·Kᵀ completed)
-          // keys [c*32, c*32+32) -> tile (c >> 1), 16-byte chunks ((c & 1) * 4 + j) ^ (r & 7)
-          uint8_t* tile = smem_aligned + P_OFF + (c >> 1) * TILE_BYTES + r * 128;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
-            *reinterpret_cast<uint4*>(tile + chunk * 16) =
-                make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
-          }
-        }
-      }
-      l_run = l_run * alpha + rowsum;
-      m_run = m_new;
-      fence_proxy_async_smem();  // P was written through the generic proxy; the MMA reads it async
-      tc_fence_before();
-      mbar_arrive(p_full);
-
-      mbar_wait(o_full, kb & 1);
-      tc_fence_after();
-      if (!SINGLE) {
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_O + lane_base + c * 32, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            o[(SINGLE ? 0 : c * 32 + j)] = o[(SINGLE ? 0 : c * 32 + j)] * alpha + __uint_as_float(v[j]);
-        }
-      }
-    }
-    const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
-    // rows past the sequence's length are pad (padded layout) or belong to the next sequence
-    // (packed layout): never written
-    __nv_bfloat16* dst = out + static_cast<size_t>(row0 + qb * QB + r) * hidden + h * HD;
-    const bool store = r < qvalid;
-    if (SINGLE) {
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_O + lane_base + c * 32, v);
-        tmem_ld_wait();
-        if (store) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 w;
-            w.x = pack_bf16x2(__uint_as_float(v[j * 8 + 0]) * inv, __uint_as_float(v[j * 8 + 1]) * inv);
-            w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
-            w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
-            w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + c * 32 + j * 8) = w;
-          }
-        }
-      }
-    } else if (store) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        uint4 w;
-        w.x = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 0)] * inv, o[(SINGLE ? 0 : j * 8 + 1)] * inv);
-        w.y = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 2)] * inv, o[(SINGLE ? 0 : j * 8 + 3)] * inv);
-        w.z = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 4)] * inv, o[(SINGLE ? 0 : j * 8 + 5)] * inv);
-        w.w = pack_bf16x2(o[(SINGLE ? 0 : j * 8 + 6)] * inv, o[(SINGLE ? 0 : j * 8 + 7)] * inv);
-        *reinterpret_cast<uint4*>(dst + j * 8) = w;
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 4) {
-    tc_fence_after();
-    tmem_dealloc<TMEM_COLS>(tmem_base);
-  }
-}
-
-// Softmax of one 128-key block for one query row, shared by the persistent kernels.
-//   tS      TMEM address of this thread's row of S (lane bits included)
-//   kvalid  keys of this block that belong to the sequence (1..128)
-//   m_run   running row maximum from earlier key blocks (-inf for the first / only block)
-//   prow    this row's 128 bytes in the first P tile (second tile at +TILE_BYTES), 128-byte swizzled
-// Returns the new maximum and the sum of exp over this block; writes P (bf16) for every 32-key chunk
-// that holds a valid key. TMEM loads are double-buffered: chunk c+1 is in flight while chunk c is
-// reduced (tcgen05.wait::ld waits for everything issued, so the next load is issued right after it).
-// A chunk that lies wholly inside the sequence takes the unmasked path: FMNMX3, packed FFMA2 / FADD2,
-// two MUFU.EX2 and one bf16x2 convert per key pair; only the chunk that straddles `kvalid` is masked.
-__device__ __forceinline__ void softmax_block(uint32_t tS, int kvalid, float sl2, float m_run, uint8_t* prow,
-                                              int r, float& m_new, float& rowsum) {
-  const int nch = (kvalid + 31) >> 5;
-  uint32_t va[32], vb[32];
+// Row maximum over this thread's half row: up to 64 keys = two 32-column TMEM chunks, one register
+// buffer (288 threads x 2 CTAs/SM leave 96 registers per thread; two buffers in flight spilled).
+// A chunk wholly inside the sequence uses FMNMX3 on key pairs.
+__device__ __forceinline__ float softmax_max64(uint32_t tS, int kv) {
   float mx = -INFINITY;
-  tmem_ld_32x32(tS, va);
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    if (c < nch) {
-      uint32_t(&cur)[32] = (c & 1) ? vb : va;
-      uint32_t(&nxt)[32] = (c & 1) ? va : vb;
+  for (int c = 0; c < 2; ++c) {
+    if (c * 32 < kv) {
+      uint32_t v[32];
+      tmem_ld_32x32(tS + c * 32, v);
       tmem_ld_wait();
-      if (c + 1 < nch) tmem_ld_32x32(tS + (c + 1) * 32, nxt);
-      if (c * 32 + 32 <= kvalid) {
+      if (c * 32 + 32 <= kv) {
 #pragma unroll
-        for (int j = 0; j < 32; j += 2)
-          mx = fmaxf(mx, fmaxf(__uint_as_float(cur[j]), __uint_as_float(cur[j + 1])));
+        for (int j = 0; j < 32; j += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(v[j]), __uint_as_float(v[j + 1])));
       } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          if (c * 32 + j < kvalid) mx = fmaxf(mx, __uint_as_float(cur[j]));
+          if (c * 32 + j < kv) mx = fmaxf(mx, __uint_as_float(v[j]));
       }
     }
   }
-  m_new = fmaxf(m_run, mx);
-  const float moff = m_new * sl2;
-  const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
-  uint64_t sum2 = f32x2(0.f, 0.f);
-  float sum1 = 0.f;
-  tmem_ld_32x32(tS, va);  // second pass, chunk 0 (the one TMEM latency per block that stays exposed)
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    if (c < nch) {
-      uint32_t(&cur)[32] = (c & 1) ? vb : va;
-      uint32_t(&nxt)[32] = (c & 1) ? va : vb;
-      uint32_t packed[16];
-      tmem_ld_wait();
-      if (c + 1 < nch) tmem_ld_32x32(tS + (c + 1) * 32, nxt);
-      if (c * 32 + 32 <= kvalid) {
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          float p0, p1;
-          f32x2_split(ffma2(f32x2_bits(cur[j], cur[j + 1]), scale2, shift2), p0, p1);
-          p0 = ex2_approx(p0);
-          p1 = ex2_approx(p1);
-          sum2 = fadd2(sum2, f32x2(p0, p1));
-          packed[j >> 1] = pack_bf16x2(p0, p1);
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          const float p0 = (c * 32 + j < kvalid) ? ex2_approx(fmaf(__uint_as_float(cur[j]), sl2, -moff)) : 0.f;
-          const float p1 =
-              (c * 32 + j + 1 < kvalid) ? ex2_approx(fmaf(__uint_as_float(cur[j + 1]), sl2, -moff)) : 0.f;
-          sum1 += p0 + p1;
-          packed[j >> 1] = pack_bf16x2(p0, p1);
-        }
-      }
-      // keys [c*32, c*32+32) -> tile (c >> 1), 16-byte chunks ((c & 1) * 4 + j) ^ (r & 7)
-      uint8_t* tile = prow + (c >> 1) * TILE_BYTES;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int chunk = (((c & 1) * 4 + j) ^ (r & 7));
-        *reinterpret_cast<uint4*>(tile + chunk * 16) =
-            make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
-      }
-    }
-  }
-  float s0, s1;
-  f32x2_split(sum2, s0, s1);
-  rowsum = sum1 + s0 + s1;
+  return mx;
 }
 
-// ---- persistent, software-pipelined variant for S = 128 (one key block per sequence) -------------
-// Two CTAs per SM, each walking (sequence, head) items i = blockIdx.x, + gridDim.x, ... with two
-// stages of {Q, K, V} tiles in shared memory and two S/O accumulators in TMEM:
-//   control thread : loads for item i+2 are in flight while item i+1's Q·Kᵀ is issued right behind
-//                    item i's P·V, so the tensor core never waits for a load and the softmax warps
-//                    never wait for Q·Kᵀ;
-//   softmax warps  : S_i (TMEM) -> P_i (smem, over the dead Q|K tiles of the same stage) ->
-//                    O_i (TMEM, over S_i) -> scaled bf16 rows to global.
-// Per-item set-up (TMEM allocation, barrier initialisation, CTA launch) is paid once per CTA
-// instead of 12,288 times per layer.
-constexpr uint32_t STAGE_BYTES_P = 3 * TILE_BYTES;
-constexpr int PERSIST_MAX_ITEMS = 256;  // (sequence, head) items one CTA may walk; the launcher sizes the grid
-constexpr uint32_t ATT_SMEM_PERSIST = 1024 + 2 * STAGE_BYTES_P + 128 + PERSIST_MAX_ITEMS * 8;
+// exp2((s - m)·c) for one 32-key chunk -> bf16 P in the swizzled tile row; returns the chunk's sum.
+// Unmasked chunks: packed FFMA2 / FADD2, two MUFU.EX2 and one bf16x2 convert per key pair.
+__device__ __forceinline__ float softmax_exp32(const uint32_t (&v)[32], int kv_chunk, float sl2, float moff,
+                                               uint8_t* tile_row, int c, int r) {
+  uint32_t packed[16];
+  float sum;
+  if (kv_chunk >= 32) {
+    const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
+    uint64_t sum2 = f32x2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      float p0, p1;
+      f32x2_split(ffma2(f32x2_bits(v[j], v[j + 1]), scale2, shift2), p0, p1);
+      p0 = ex2_approx(p0);
+      p1 = ex2_approx(p1);
+      sum2 = fadd2(sum2, f32x2(p0, p1));
+      packed[j >> 1] = pack_bf16x2(p0, p1);
+    }
+    float s0, s1;
+    f32x2_split(sum2, s0, s1);
+    sum = s0 + s1;
+  } else {
+    sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      const float p0 = (j < kv_chunk) ? ex2_approx(fmaf(__uint_as_float(v[j]), sl2, -moff)) : 0.f;
+      const float p1 = (j + 1 < kv_chunk) ? ex2_approx(fmaf(__uint_as_float(v[j + 1]), sl2, -moff)) : 0.f;
+      sum += p0 + p1;
+      packed[j >> 1] = pack_bf16x2(p0, p1);
+    }
+  }
+  // chunk c (0/1) of this 64-key tile -> 16-byte slots (4c + j) ^ (r & 7) of the 128-byte row
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int slot = ((c * 4 + j) ^ (r & 7));
+    *reinterpret_cast<uint4*>(tile_row + slot * 16) =
+        make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
+  }
+  return sum;
+}
 
+// P for this thread's half row (up to 64 keys) given the row maximum; returns the half row's sum.
+__device__ __forceinline__ float softmax_exp64(uint32_t tS, int kv, float sl2, float m_new, uint8_t* tile_row,
+                                               int r) {
+  const float moff = m_new * sl2;
+  float sum = 0.f;
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    if (c * 32 < kv) {
+      uint32_t v[32];
+      tmem_ld_32x32(tS + c * 32, v);
+      tmem_ld_wait();
+      sum += softmax_exp32(v, kv - c * 32, sl2, moff, tile_row, c, r);
+    }
+  }
+  return sum;
+}
+
+// ================================================================================================
+// S = 128: one item = (sequence, head)
+// ================================================================================================
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
                          const int32_t* __restrict__ lens, int S, int hidden, int heads, int n_items,
                          const int32_t* __restrict__ cu, unsigned long long* __restrict__ trace) {
   // developer timeline (dev_check "atttrace"): CTA 0 records %globaltimer at each pipeline event of
   // its first 64 items: [item][0..3] control thread (P seen, PV committed, O seen, load issued),
-  // [item][4..7] softmax row 0 (S seen, P arrived, O seen, row stored)
+  // [item][4..7] softmax thread 0 (S seen, P arrived, O seen, row stored)
   auto stamp = [&](int item, int slot) {
     if (trace && blockIdx.x == 0 && item < 64) {
       unsigned long long t;
@@ -365,23 +165,18 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t bars = base + 2 * STAGE_BYTES_P;
-  // per stage s: qkv_full, s_full, p_full, o_full, free
+  const uint32_t bars = base + OFF_BARS;
   auto bar = [&](int which, int s) { return bars + 8u * (which * 2 + s); };
-  enum { QKV_FULL = 0, S_FULL = 1, P_FULL = 2, O_FULL = 3, FREE = 4 };
   const uint32_t tmem_slot = bars + 8u * 10;
   uint8_t* smem_aligned = smem_raw + (base - raw);
-  volatile uint32_t* tmem_slot_ptr =
-      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_aligned + OFF_BARS + 80);
+  float* red = reinterpret_cast<float*>(smem_aligned + OFF_RED);
+  int2* meta = reinterpret_cast<int2*>(smem_aligned + OFF_META);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int my_items = (n_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                        static_cast<int>(gridDim.x);
-  // Per-item (length, first row) looked up ONCE into shared memory: the control thread's loop is a
-  // chain of dependent steps, and a global load of lens[] / cu[] in it costs ~0.5 us each time
-  // (measured with the dev_check timeline: 2 us of a 4.8 us item were such loads).
-  int2* meta = reinterpret_cast<int2*>(smem_aligned + 2 * STAGE_BYTES_P + 128);
   for (int i = threadIdx.x; i < my_items; i += blockDim.x) {
     const int idx = blockIdx.x + i * gridDim.x;
     const int b = idx / heads;
@@ -390,52 +185,50 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
     meta[i] = make_int2(len, cu ? cu[b] : b * S);
   }
 
-  if (threadIdx.x == 128) {
+  if (threadIdx.x == ATT_SOFTMAX_THREADS) {
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar(QKV_FULL, s), 1);
       mbar_init(bar(S_FULL, s), 1);
-      mbar_init(bar(P_FULL, s), 128);
+      mbar_init(bar(P_FULL, s), ATT_SOFTMAX_THREADS);
       mbar_init(bar(O_FULL, s), 1);
-      mbar_init(bar(FREE, s), 128);
+      mbar_init(bar(FREE, s), ATT_SOFTMAX_THREADS);
     }
     fence_barrier_init();
   }
-  if (warp == 4) tmem_alloc<256>(tmem_slot);
+  if (warp == 8) tmem_alloc<256>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
       auto load_item = [&](int i) {
         const int idx = blockIdx.x + i * gridDim.x;
         const int h = idx % heads;
         const int2 md = meta[i];
-        const int row0 = md.y;
         const int box = (md.x + 31) >> 5;
         const int s = i & 1;
-        const uint32_t st = base + s * STAGE_BYTES_P;
+        const uint32_t st = base + s * STAGE_BYTES;
         mbar_expect_tx(bar(QKV_FULL, s), 3 * box * 32 * 128);
-        tma_load_2d(st, &maps.m[box - 1], bar(QKV_FULL, s), h * HD, row0);
-        tma_load_2d(st + TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), hidden + h * HD, row0);
-        tma_load_2d(st + 2 * TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), 2 * hidden + h * HD, row0);
+        tma_load_2d(st, &maps.m[box - 1], bar(QKV_FULL, s), h * HD, md.y);
+        tma_load_2d(st + TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), hidden + h * HD, md.y);
+        tma_load_2d(st + 2 * TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), 2 * hidden + h * HD, md.y);
       };
       // pull item i's tiles from DRAM into L2 ahead of its TMA load (no shared memory needed)
       auto prefetch_item = [&](int i) {
         const int idx = blockIdx.x + i * gridDim.x;
         const int h = idx % heads;
         const int2 md = meta[i];
-        const int row0 = md.y;
         const int box = (md.x + 31) >> 5;
-        tma_prefetch_2d(&maps.m[box - 1], h * HD, row0);
-        tma_prefetch_2d(&maps.m[box - 1], hidden + h * HD, row0);
-        tma_prefetch_2d(&maps.m[box - 1], 2 * hidden + h * HD, row0);
+        tma_prefetch_2d(&maps.m[box - 1], h * HD, md.y);
+        tma_prefetch_2d(&maps.m[box - 1], hidden + h * HD, md.y);
+        tma_prefetch_2d(&maps.m[box - 1], 2 * hidden + h * HD, md.y);
       };
       auto nk_of = [&](int i) { return ((meta[i].x + 31) >> 5) * 32; };
       auto issue_s = [&](int i) {
         const int s = i & 1;
-        const uint32_t st = base + s * STAGE_BYTES_P;
+        const uint32_t st = base + s * STAGE_BYTES;
         mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
         tc_fence_after();
         const uint32_t idesc_s = umma_idesc_bf16(128, nk_of(i), 0, 0);
@@ -454,14 +247,16 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       for (int i = 0; i < my_items; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;
-        const uint32_t st = base + s * STAGE_BYTES_P;
+        const uint32_t st = base + s * STAGE_BYTES;
         const int nk = nk_of(i);
         mbar_wait(bar(P_FULL, s), ph);
         stamp(i, 0);
         tc_fence_after();
         constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
         for (int k = 0; k < nk / 16; ++k) {
+          // A = P: K-major, 64 keys per 16 KiB tile, 32 bytes per K=16 step inside the swizzle atom
           const uint64_t pd = umma_desc_sw128(st + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
+          // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes per step
           const uint64_t vd = umma_desc_sw128(st + 2 * TILE_BYTES + k * 2048, 8192, 1024);
           umma_bf16(tmem_base + s * 128, pd, vd, idesc_o, k != 0);
         }
@@ -481,9 +276,12 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       }
     }
   } else {
-    const int r = threadIdx.x;
-    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    const int r = threadIdx.x & 127;    // query row
+    const int half = threadIdx.x >> 7;  // keys [64*half, +64), output columns [32*half, +32)
+    const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
+    float* red_max = red;
+    float* red_sum = red + 256;
     for (int i = 0; i < my_items; ++i) {
       const int s = i & 1;
       const uint32_t ph = (i >> 1) & 1;
@@ -491,29 +289,36 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       const int h = idx % heads;
       const int2 md = meta[i];
       const int len = md.x, row0 = md.y;
+      const int kv = min(64, max(0, len - 64 * half));  // valid keys in this thread's half row
       const uint32_t tS = tmem_base + s * 128 + lane_base;
+      uint8_t* tile_row = smem_aligned + s * STAGE_BYTES + half * TILE_BYTES + r * 128;
       mbar_wait(bar(S_FULL, s), ph);
-      if (r == 0) stamp(i, 4);
+      if (threadIdx.x == 0) stamp(i, 4);
       tc_fence_after();
-      float m_new, rowsum;
-      softmax_block(tS, len, sl2, -INFINITY, smem_aligned + s * STAGE_BYTES_P + r * 128, r, m_new, rowsum);
-      fence_proxy_async_smem();
+      float mx = kv > 0 ? softmax_max64(tS + 64 * half, kv) : -INFINITY;
+      red_max[half * 128 + r] = mx;
+      softmax_bar();
+      mx = fmaxf(mx, red_max[(half ^ 1) * 128 + r]);
+      float rowsum = kv > 0 ? softmax_exp64(tS + 64 * half, kv, sl2, mx, tile_row, r) : 0.f;
+      red_sum[half * 128 + r] = rowsum;
+      fence_proxy_async_smem();  // P was written through the generic proxy; the MMA reads it async
       tc_fence_before();
       mbar_arrive(bar(P_FULL, s));
-      if (r == 0) stamp(i, 5);
-
+      if (threadIdx.x == 0) stamp(i, 5);
+      softmax_bar();
+      rowsum += red_sum[(half ^ 1) * 128 + r];
       const float inv = rowsum > 0.f ? 1.0f / rowsum : 0.f;
-      __nv_bfloat16* dst = out + static_cast<size_t>(row0 + r) * hidden + h * HD;
-      const bool store = r < len;
+      // rows past the sequence's length are pad (padded layout) or belong to the next sequence
+      // (packed layout): never written
+      __nv_bfloat16* dst = out + static_cast<size_t>(row0 + r) * hidden + h * HD + half * 32;
       mbar_wait(bar(O_FULL, s), ph);
-      if (r == 0) stamp(i, 6);
+      if (threadIdx.x == 0) stamp(i, 6);
       tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      {
         uint32_t v[32];
-        tmem_ld_32x32(tS + c * 32, v);
+        tmem_ld_32x32(tS + half * 32, v);
         tmem_ld_wait();
-        if (store) {
+        if (r < len) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 w;
@@ -521,32 +326,30 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
             w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
             w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
             w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + c * 32 + j * 8) = w;
+            *reinterpret_cast<uint4*>(dst + j * 8) = w;
           }
         }
       }
       tc_fence_before();
       mbar_arrive(bar(FREE, s));
-      if (r == 0) stamp(i, 7);
+      if (threadIdx.x == 0) stamp(i, 7);
     }
   }
 
   __syncwarp();
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc<256>(tmem_base);
   }
 }
 
-// ---- persistent variant for S = 256 .. 512 (several key blocks per query block) ------------------
-// Same ring as attention_persist_kernel, but a ring step is one (sequence, head, query block, key
-// block): Q is re-fetched with every key block (an L2 hit; it lets P overlay the Q|K tiles exactly as
-// in the one-block kernel), and the softmax threads carry the running maximum, denominator and the
-// f32 output row across the key blocks of a query block (online softmax), writing the row once.
+// ================================================================================================
+// S = 256 .. 512: one ring step = (sequence, head, query block, key block)
+// ================================================================================================
 struct AttStep {
-  int item, kb, nkb, b, h, qb, len, row0;
+  int item, kb, nkb, h, qb, len, row0;
   bool valid;
 };
 
@@ -560,14 +363,14 @@ __device__ __forceinline__ void att_step_next(AttStep& it, const int32_t* __rest
     int t = it.item;
     it.qb = t % qblocks; t /= qblocks;
     it.h = t % heads;
-    it.b = t / heads;
-    int len = lens[it.b];
+    const int b = t / heads;
+    int len = lens[b];
     len = len < 0 ? 0 : (len > S ? S : len);
     if (it.qb * QB >= len) continue;  // query block of pad rows only
     it.len = len;
     it.nkb = (len + KB - 1) / KB;
     it.kb = 0;
-    it.row0 = cu ? cu[it.b] : it.b * S;
+    it.row0 = cu ? cu[b] : b * S;
     return;
   }
 }
@@ -587,41 +390,40 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t bars = base + 2 * STAGE_BYTES_P;
+  const uint32_t bars = base + OFF_BARS;
   auto bar = [&](int which, int s) { return bars + 8u * (which * 2 + s); };
-  enum { QKV_FULL = 0, S_FULL = 1, P_FULL = 2, O_FULL = 3, FREE = 4 };
   const uint32_t tmem_slot = bars + 8u * 10;
   uint8_t* smem_aligned = smem_raw + (base - raw);
-  volatile uint32_t* tmem_slot_ptr =
-      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_aligned + OFF_BARS + 80);
+  float* red = reinterpret_cast<float*>(smem_aligned + OFF_RED);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  if (threadIdx.x == 128) {
+  if (threadIdx.x == ATT_SOFTMAX_THREADS) {
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar(QKV_FULL, s), 1);
       mbar_init(bar(S_FULL, s), 1);
-      mbar_init(bar(P_FULL, s), 128);
+      mbar_init(bar(P_FULL, s), ATT_SOFTMAX_THREADS);
       mbar_init(bar(O_FULL, s), 1);
-      mbar_init(bar(FREE, s), 128);
+      mbar_init(bar(FREE, s), ATT_SOFTMAX_THREADS);
     }
     fence_barrier_init();
   }
-  if (warp == 4) tmem_alloc<256>(tmem_slot);
+  if (warp == 8) tmem_alloc<256>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
       auto kbox_of = [&](const AttStep& it) { return (min(KB, it.len - it.kb * KB) + 31) >> 5; };
       auto load_step = [&](const AttStep& it, int i) {
         const int qbox = (min(QB, it.len - it.qb * QB) + 31) >> 5;
         const int kbox = kbox_of(it);
         const int s = i & 1;
-        const uint32_t st = base + s * STAGE_BYTES_P;
+        const uint32_t st = base + s * STAGE_BYTES;
         mbar_expect_tx(bar(QKV_FULL, s), (qbox + 2 * kbox) * 32 * 128);
         tma_load_2d(st, &maps.m[qbox - 1], bar(QKV_FULL, s), it.h * HD, it.row0 + it.qb * QB);
         tma_load_2d(st + TILE_BYTES, &maps.m[kbox - 1], bar(QKV_FULL, s), hidden + it.h * HD,
@@ -631,7 +433,7 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
       };
       auto issue_s = [&](const AttStep& it, int i) {
         const int s = i & 1;
-        const uint32_t st = base + s * STAGE_BYTES_P;
+        const uint32_t st = base + s * STAGE_BYTES;
         mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
         tc_fence_after();
         const uint32_t idesc_s = umma_idesc_bf16(128, kbox_of(it) * 32, 0, 0);
@@ -651,7 +453,7 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
       for (int i = 0; pv.valid; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;
-        const uint32_t st = base + s * STAGE_BYTES_P;
+        const uint32_t st = base + s * STAGE_BYTES;
         const int nk = kbox_of(pv) * 32;
         mbar_wait(bar(P_FULL, s), ph);
         tc_fence_after();
@@ -664,7 +466,7 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
         umma_commit(bar(O_FULL, s));
         if (si.valid) { issue_s(si, i + 1); att_step_next(si, lens, cu, S, heads, qblocks, n_items); }
         if (ld.valid) {
-          mbar_wait(bar(FREE, s), ph);
+          mbar_wait(bar(O_FULL, s), ph);  // smem of stage s is free once P·V(i) has completed
           load_step(ld, i + 2);
           att_step_next(ld, lens, cu, S, heads, qblocks, n_items);
         }
@@ -672,11 +474,14 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
       }
     }
   } else {
-    const int r = threadIdx.x;
-    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    const int r = threadIdx.x & 127;
+    const int half = threadIdx.x >> 7;
+    const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
+    float* red_max = red;
+    float* red_sum = red + 256;
     float m_run = -INFINITY, l_run = 0.f;
-    float o[HD];
+    float o[32];  // this thread's 32 output columns of its row, f32, rescaled block by block
     AttStep it;
     att_step_init(it, lens, cu, S, heads, qblocks, n_items);
     for (int i = 0; it.valid; ++i) {
@@ -685,30 +490,38 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
       if (it.kb == 0) {
         m_run = -INFINITY; l_run = 0.f;
 #pragma unroll
-        for (int e = 0; e < HD; ++e) o[e] = 0.f;
+        for (int e = 0; e < 32; ++e) o[e] = 0.f;
       }
       const int kvalid = min(KB, it.len - it.kb * KB);
+      const int kv = min(64, max(0, kvalid - 64 * half));
       const uint32_t tS = tmem_base + s * 128 + lane_base;
+      uint8_t* tile_row = smem_aligned + s * STAGE_BYTES + half * TILE_BYTES + r * 128;
       mbar_wait(bar(S_FULL, s), ph);
       tc_fence_after();
-      float m_new, rowsum;
-      softmax_block(tS, kvalid, sl2, m_run, smem_aligned + s * STAGE_BYTES_P + r * 128, r, m_new, rowsum);
-      const float alpha = ex2_approx((m_run - m_new) * sl2);
-      l_run = l_run * alpha + rowsum;
-      m_run = m_new;
+      float mx = kv > 0 ? softmax_max64(tS + 64 * half, kv) : -INFINITY;
+      red_max[half * 128 + r] = mx;
+      softmax_bar();
+      mx = fmaxf(mx, red_max[(half ^ 1) * 128 + r]);
+      const float m_new = fmaxf(m_run, mx);
+      float rowsum = kv > 0 ? softmax_exp64(tS + 64 * half, kv, sl2, m_new, tile_row, r) : 0.f;
+      red_sum[half * 128 + r] = rowsum;
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(bar(P_FULL, s));
+      softmax_bar();
+      rowsum += red_sum[(half ^ 1) * 128 + r];
+      const float alpha = ex2_approx((m_run - m_new) * sl2);
+      l_run = l_run * alpha + rowsum;
+      m_run = m_new;
 
       mbar_wait(bar(O_FULL, s), ph);
       tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      {
         uint32_t v[32];
-        tmem_ld_32x32(tS + c * 32, v);
+        tmem_ld_32x32(tS + half * 32, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; ++j) o[c * 32 + j] = fmaf(o[c * 32 + j], alpha, __uint_as_float(v[j]));
+        for (int j = 0; j < 32; ++j) o[j] = fmaf(o[j], alpha, __uint_as_float(v[j]));
       }
       tc_fence_before();
       mbar_arrive(bar(FREE, s));
@@ -717,9 +530,10 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
         const int qvalid = min(QB, it.len - it.qb * QB);
         if (r < qvalid) {
           const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
-          __nv_bfloat16* dst = out + static_cast<size_t>(it.row0 + it.qb * QB + r) * hidden + it.h * HD;
+          __nv_bfloat16* dst =
+              out + static_cast<size_t>(it.row0 + it.qb * QB + r) * hidden + it.h * HD + half * 32;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
+          for (int j = 0; j < 4; ++j) {
             uint4 w;
             w.x = pack_bf16x2(o[j * 8 + 0] * inv, o[j * 8 + 1] * inv);
             w.y = pack_bf16x2(o[j * 8 + 2] * inv, o[j * 8 + 3] * inv);
@@ -736,7 +550,7 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
   __syncwarp();
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc<256>(tmem_base);
   }
@@ -770,46 +584,31 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
   int dev = 0;
   B2_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 64 && !configured[dev]) {
-    B2_CUDA_OK(cudaFuncSetAttribute(attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    ATT_SMEM_SINGLE));
-    B2_CUDA_OK(cudaFuncSetAttribute(attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    ATT_SMEM_MULTI));
     B2_CUDA_OK(cudaFuncSetAttribute(attention_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    ATT_SMEM_PERSIST));
+                                    ATT_SMEM));
     B2_CUDA_OK(cudaFuncSetAttribute(attention_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    ATT_SMEM_PERSIST));
+                                    ATT_SMEM));
     configured[dev] = true;
   }
   const int heads = hidden / HD, qblocks = S / QB;
-  const long long grid = 1ll * B * heads * qblocks;
-  if (grid > 0x7fffffffll) {
-    set_last_error("attention_bf16: grid too large");
+  const long long items = 1ll * B * heads * qblocks;
+  if (items > 0x7fffffffll) {
+    set_last_error("attention_bf16: too many work items");
     return B2_ERR_ARG;
   }
+  int sms = 0;
+  B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const AttMaps& maps = reinterpret_cast<const AttMaps&>(tqkv);
-  static const bool one_shot = [] { const char* e = getenv("B2_ATTN_ONESHOT"); return e && e[0] == '1'; }();
-  if (S == QB && !one_shot) {
-    int sms = 0;
-    B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int items = B * heads;
-    int ctas = items < 2 * sms ? items : 2 * sms;
-    const int need = (items + PERSIST_MAX_ITEMS - 1) / PERSIST_MAX_ITEMS;  // keep a CTA's item list in smem
-    if (ctas < need) ctas = need;
-    attention_persist_kernel<<<ctas, ATT_THREADS, ATT_SMEM_PERSIST, stream>>>(maps, out, lens, S, hidden,
-                                                                             heads, items, cu, g_att_trace);
-  } else if (!one_shot) {
-    int sms = 0;
-    B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int items = static_cast<int>(grid);
-    const int ctas = items < 2 * sms ? items : 2 * sms;
-    attention_stream_kernel<<<ctas, ATT_THREADS, ATT_SMEM_PERSIST, stream>>>(maps, out, lens, S, hidden, heads,
-                                                                            qblocks, items, cu);
-  } else if (S == QB)
-    attention_kernel<true><<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM_SINGLE, stream>>>(
-        maps, out, lens, S, hidden, heads, qblocks, cu);
-  else
-    attention_kernel<false><<<static_cast<unsigned>(grid), ATT_THREADS, ATT_SMEM_MULTI, stream>>>(
-        maps, out, lens, S, hidden, heads, qblocks, cu);
+  int ctas = items < 2 * sms ? static_cast<int>(items) : 2 * sms;
+  if (S == QB) {
+    const int need = static_cast<int>((items + PERSIST_MAX_ITEMS - 1) / PERSIST_MAX_ITEMS);
+    if (ctas < need) ctas = need;  // a CTA's item list must fit its shared-memory table
+    attention_persist_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(maps, out, lens, S, hidden, heads,
+                                                                      static_cast<int>(items), cu, g_att_trace);
+  } else {
+    attention_stream_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(maps, out, lens, S, hidden, heads, qblocks,
+                                                                     static_cast<int>(items), cu);
+  }
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }
