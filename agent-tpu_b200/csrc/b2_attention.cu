@@ -11,11 +11,13 @@
 // and 128 rows), the UMMA N of Q·Kᵀ and the K extent of P·V all shrink with the sequence. Rows of
 // the tiles beyond the box hold stale shared memory; no MMA whose result is kept reads them.
 //
-//   control thread : item i+1's Q·Kᵀ is issued right behind item i's P·V and item i+2's loads go out
-//                    as soon as P·V(i) has completed (tiles two further ahead are prefetched into L2),
-//                    so the tensor core never waits for a load and the softmax warps never wait for
-//                    Q·Kᵀ. Per-item (length, first row) are looked up once into shared memory: a
-//                    global load in this thread's dependent chain costs ~0.5 us each time.
+//   MMA thread     : item i+1's Q·Kᵀ is issued right behind item i's P·V, so the softmax warps never
+//                    wait for Q·Kᵀ.
+//   TMA thread     : item i+2's loads go out as soon as P·V(i) has completed (tiles two further ahead
+//                    are prefetched into L2). Two single-thread roles in two warps, because one
+//                    thread doing both spent 0.8 us per item issuing (dev_check timeline), and
+//                    per-item (length, first row) are looked up once into shared memory: a global
+//                    load in such a dependent chain costs ~0.5 us each time.
 //   softmax warps  : eight per CTA, two threads per query row (keys 0-63 / 64-127, then output columns
 //                    0-31 / 32-63); the row maximum and denominator are exchanged through shared
 //                    memory. This part is a chain of TMEM loads, MUFU.EX2 and row-strided stores: it
@@ -40,7 +42,7 @@ namespace b2 {
 
 namespace {
 
-constexpr int ATT_THREADS = 288;  // warps 0-7: softmax (2 threads per query row); warp 8: TMA + MMA issue
+constexpr int ATT_THREADS = 320;  // warps 0-7: softmax (2 threads per query row); warp 8: MMA issue; warp 9: TMA
 constexpr int ATT_SOFTMAX_THREADS = 256;
 constexpr int QB = 128;  // queries per item / step
 constexpr int KB = 128;  // keys per block
@@ -153,7 +155,8 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
                          const int32_t* __restrict__ lens, int S, int hidden, int heads, int n_items,
                          const int32_t* __restrict__ cu, unsigned long long* __restrict__ trace) {
   // developer timeline (dev_check "atttrace"): CTA 0 records %globaltimer at each pipeline event of
-  // its first 64 items: [item][0..3] control thread (P seen, PV committed, O seen, load issued),
+  // its first 64 items: [item][0..1] MMA thread (P seen, P·V and next Q·Kᵀ issued), [item][3] TMA thread
+  // (next-next loads issued),
   // [item][4..7] softmax thread 0 (S seen, P arrived, O seen, row stored)
   auto stamp = [&](int item, int slot) {
     if (trace && blockIdx.x == 0 && item < 64) {
@@ -201,7 +204,8 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  if (warp == 8) {
+  if (warp == 9) {
+    // ===== TMA thread =====
     if (lane == 0) {
       auto load_item = [&](int i) {
         const int idx = blockIdx.x + i * gridDim.x;
@@ -225,54 +229,60 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
         tma_prefetch_2d(&maps.m[box - 1], hidden + h * HD, md.y);
         tma_prefetch_2d(&maps.m[box - 1], 2 * hidden + h * HD, md.y);
       };
-      auto nk_of = [&](int i) { return ((meta[i].x + 31) >> 5) * 32; };
+      if (my_items > 0) load_item(0);
+      if (my_items > 1) load_item(1);
+      if (my_items > 2) prefetch_item(2);
+      if (my_items > 3) prefetch_item(3);
+      for (int i = 0; i + 2 < my_items; ++i) {
+        // stage s's shared memory is free as soon as P·V(i) has completed; its TMEM columns are only
+        // needed again by S(i+2), which the MMA thread issues after P_FULL(i+1), i.e. after the
+        // softmax threads have read O(i)
+        mbar_wait(bar(O_FULL, i & 1), (i >> 1) & 1);
+        load_item(i + 2);
+        if (i + 4 < my_items) prefetch_item(i + 4);
+        stamp(i, 3);
+      }
+    }
+  } else if (warp == 8) {
+    // ===== MMA thread =====
+    if (lane == 0) {
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
       auto issue_s = [&](int i) {
         const int s = i & 1;
         const uint32_t st = base + s * STAGE_BYTES;
-        mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
-        tc_fence_after();
-        const uint32_t idesc_s = umma_idesc_bf16(128, nk_of(i), 0, 0);
+        const int nk = ((meta[i].x + 31) >> 5) * 32;
+        const uint32_t idesc_s = umma_idesc_bf16(128, nk, 0, 0);
         const uint64_t qd = umma_desc_sw128(st, 16, 1024);
         const uint64_t kd = umma_desc_sw128(st + TILE_BYTES, 16, 1024);
+        mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
+        tc_fence_after();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
           umma_bf16(tmem_base + s * 128, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
         umma_commit(bar(S_FULL, s));
       };
-      if (my_items > 0) load_item(0);
-      if (my_items > 1) load_item(1);
-      if (my_items > 2) prefetch_item(2);
-      if (my_items > 3) prefetch_item(3);
       if (my_items > 0) issue_s(0);
       for (int i = 0; i < my_items; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;
         const uint32_t st = base + s * STAGE_BYTES;
-        const int nk = nk_of(i);
+        const int nk16 = (meta[i].x + 31) >> 5 << 1;  // K=16 steps of P·V: keys rounded up to 32, / 16
+        // A = P: K-major, 64 keys per 16 KiB tile, 32 bytes per K=16 step inside the swizzle atom
+        const uint64_t pd0 = umma_desc_sw128(st, 16, 1024);
+        // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes (>>4 = 128) per step
+        const uint64_t vd0 = umma_desc_sw128(st + 2 * TILE_BYTES, 8192, 1024);
         mbar_wait(bar(P_FULL, s), ph);
         stamp(i, 0);
         tc_fence_after();
-        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
-        for (int k = 0; k < nk / 16; ++k) {
-          // A = P: K-major, 64 keys per 16 KiB tile, 32 bytes per K=16 step inside the swizzle atom
-          const uint64_t pd = umma_desc_sw128(st + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
-          // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes per step
-          const uint64_t vd = umma_desc_sw128(st + 2 * TILE_BYTES + k * 2048, 8192, 1024);
-          umma_bf16(tmem_base + s * 128, pd, vd, idesc_o, k != 0);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (k < nk16)
+            umma_bf16(tmem_base + s * 128, pd0 + ((k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2), vd0 + k * 128u,
+                      idesc_o, k != 0);
         }
         umma_commit(bar(O_FULL, s));
         if (i + 1 < my_items) issue_s(i + 1);  // right behind P·V: the softmax warps find S ready
         stamp(i, 1);
-        if (i + 2 < my_items) {
-          // stage s's shared memory is free as soon as P·V(i) has completed; its TMEM columns are
-          // only needed again by S(i+2), which is issued one iteration later, after the softmax
-          // threads have read O(i) (they arrive on P_FULL(i+1) only after that read)
-          mbar_wait(bar(O_FULL, s), ph);
-          stamp(i, 2);
-          load_item(i + 2);
-          if (i + 4 < my_items) prefetch_item(i + 4);
-          stamp(i, 3);
-        }
       }
     }
   } else {
@@ -416,9 +426,10 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  if (warp == 8) {
+  auto kbox_of = [&](const AttStep& it) { return (min(KB, it.len - it.kb * KB) + 31) >> 5; };
+  if (warp == 9) {
+    // ===== TMA thread =====
     if (lane == 0) {
-      auto kbox_of = [&](const AttStep& it) { return (min(KB, it.len - it.kb * KB) + 31) >> 5; };
       auto load_step = [&](const AttStep& it, int i) {
         const int qbox = (min(QB, it.len - it.qb * QB) + 31) >> 5;
         const int kbox = kbox_of(it);
@@ -431,45 +442,54 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
         tma_load_2d(st + 2 * TILE_BYTES, &maps.m[kbox - 1], bar(QKV_FULL, s), 2 * hidden + it.h * HD,
                     it.row0 + it.kb * KB);
       };
+      AttStep ld;
+      att_step_init(ld, lens, cu, S, heads, qblocks, n_items);
+      if (ld.valid) { load_step(ld, 0); att_step_next(ld, lens, cu, S, heads, qblocks, n_items); }
+      if (ld.valid) { load_step(ld, 1); att_step_next(ld, lens, cu, S, heads, qblocks, n_items); }
+      for (int i = 0; ld.valid; ++i) {
+        mbar_wait(bar(O_FULL, i & 1), (i >> 1) & 1);  // smem of the stage is free once P·V(i) has completed
+        load_step(ld, i + 2);
+        att_step_next(ld, lens, cu, S, heads, qblocks, n_items);
+      }
+    }
+  } else if (warp == 8) {
+    // ===== MMA thread =====
+    if (lane == 0) {
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
       auto issue_s = [&](const AttStep& it, int i) {
         const int s = i & 1;
         const uint32_t st = base + s * STAGE_BYTES;
-        mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
-        tc_fence_after();
         const uint32_t idesc_s = umma_idesc_bf16(128, kbox_of(it) * 32, 0, 0);
         const uint64_t qd = umma_desc_sw128(st, 16, 1024);
         const uint64_t kd = umma_desc_sw128(st + TILE_BYTES, 16, 1024);
+        mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
+        tc_fence_after();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
           umma_bf16(tmem_base + s * 128, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
         umma_commit(bar(S_FULL, s));
       };
-      AttStep ld, si, pv;
-      att_step_init(ld, lens, cu, S, heads, qblocks, n_items);
-      si = ld; pv = ld;
-      if (ld.valid) { load_step(ld, 0); att_step_next(ld, lens, cu, S, heads, qblocks, n_items); }
-      if (ld.valid) { load_step(ld, 1); att_step_next(ld, lens, cu, S, heads, qblocks, n_items); }
+      AttStep si, pv;
+      att_step_init(si, lens, cu, S, heads, qblocks, n_items);
+      pv = si;
       if (si.valid) { issue_s(si, 0); att_step_next(si, lens, cu, S, heads, qblocks, n_items); }
       for (int i = 0; pv.valid; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;
         const uint32_t st = base + s * STAGE_BYTES;
-        const int nk = kbox_of(pv) * 32;
+        const int nk16 = kbox_of(pv) << 1;
+        const uint64_t pd0 = umma_desc_sw128(st, 16, 1024);
+        const uint64_t vd0 = umma_desc_sw128(st + 2 * TILE_BYTES, 8192, 1024);
         mbar_wait(bar(P_FULL, s), ph);
         tc_fence_after();
-        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
-        for (int k = 0; k < nk / 16; ++k) {
-          const uint64_t pd = umma_desc_sw128(st + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024);
-          const uint64_t vd = umma_desc_sw128(st + 2 * TILE_BYTES + k * 2048, 8192, 1024);
-          umma_bf16(tmem_base + s * 128, pd, vd, idesc_o, k != 0);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (k < nk16)
+            umma_bf16(tmem_base + s * 128, pd0 + ((k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2), vd0 + k * 128u,
+                      idesc_o, k != 0);
         }
         umma_commit(bar(O_FULL, s));
         if (si.valid) { issue_s(si, i + 1); att_step_next(si, lens, cu, S, heads, qblocks, n_items); }
-        if (ld.valid) {
-          mbar_wait(bar(O_FULL, s), ph);  // smem of stage s is free once P·V(i) has completed
-          load_step(ld, i + 2);
-          att_step_next(ld, lens, cu, S, heads, qblocks, n_items);
-        }
         att_step_next(pv, lens, cu, S, heads, qblocks, n_items);
       }
     }

@@ -71,6 +71,29 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Non-suspending probe (mbarrier.test_wait) and a polling wait built on it. try_wait parks the thread
+// for a system-defined period when the phase is not complete yet; for waits that are about to be
+// satisfied by a tcgen05.commit arrival that period (~1 us, dev_check timeline) is far longer than
+// the wait itself, so latency-critical waiters poll instead.
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_poll(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_test_wait(bar, parity)) {
+    if (++spins > (1u << 28)) __trap();
+  }
+}
 // Bounded wait: a pipeline bug must surface as a trapped launch (cudaErrorLaunchFailure on the
 // host), never as a hung GPU. try_wait itself sleeps in hardware for a bounded time per probe,
 // so the bound below is between ~50 ms and a few seconds of wall clock, far beyond any legitimate wait.
