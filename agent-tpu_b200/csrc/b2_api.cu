@@ -967,6 +967,11 @@ static OutLayout out_layout(int64_t n, int topk, int C, bool want_logits) {
   return L;
 }
 
+static int classify_to_host(b2_handle* h, const uint8_t* d_text, const int64_t* d_off, const int32_t* d_ids,
+                            const uint8_t* d_mask, int64_t n, int32_t max_len, int32_t topk,
+                            int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
+                            float* logits, b2_metrics* metrics, int64_t h2d);
+
 static int classify_host(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, const int32_t* ids,
                          const uint8_t* mask, int64_t n, int32_t max_len, int32_t topk,
                          int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
@@ -1005,6 +1010,18 @@ static int classify_host(b2_handle* h, const uint8_t* utf8, const int64_t* offse
     d_mask = h->st_text + ib;
     h2d = ib + mb;
   }
+  return classify_to_host(h, d_text, d_off, d_ids, d_mask, n, max_len, topk, top_idx, top_score, labels,
+                          histogram, logits, metrics, h2d);
+}
+
+// Run classify_device with the outputs staged in device memory, then copy them to the caller's host
+// buffers. Inputs are device pointers; the caller holds the handle's lock and has checked topk.
+static int classify_to_host(b2_handle* h, const uint8_t* d_text, const int64_t* d_off, const int32_t* d_ids,
+                            const uint8_t* d_mask, int64_t n, int32_t max_len, int32_t topk,
+                            int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
+                            float* logits, b2_metrics* metrics, int64_t h2d) {
+  int rc;
+  const int C = h->mh.num_labels;
   const OutLayout L = out_layout(n, topk, C, logits != nullptr);
   if ((rc = grow(&h->st_out, &h->st_out_cap, L.total))) return rc;
   uint8_t* ob = static_cast<uint8_t*>(h->st_out);
@@ -1082,6 +1099,349 @@ int b2_chunk_bounds(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, i
   B2_CUDA_OK(cudaStreamSynchronize(h->stream));
   if (n_chunks) B2_CUDA_OK(cudaMemcpy(bounds, d_bounds, size_t(n_chunks) * 8, cudaMemcpyDeviceToHost));
   return B2_OK;
+}
+
+}  // extern "C"
+
+// ================================================================================================
+// CSV: row index, field extraction and the csv -> tokenize -> classify chain
+// ================================================================================================
+// Counterpart of _read_csv_shard (ops/csv_shard.py:9-26). The reference re-parses the file from the
+// top with csv.DictReader for every shard; here the file is indexed once (b2_csv_open) and shards
+// are cut from the index.
+
+struct b2_csv {
+  b2_handle* h = nullptr;
+  uint8_t* d_bytes = nullptr;
+  int64_t n = 0, data_offset = 0, rows = 0;
+  int64_t *row_start = nullptr, *row_end = nullptr;
+  bool has_header = false;
+  std::string header_bytes;         // unquoted header names back to back
+  std::vector<int64_t> header_end;  // end offset of every name in header_bytes
+  // result of the last sizing pass, reused by b2_csv_rows_read
+  int64_t sz_start = -1, sz_rows = -1, sz_fields = 0, sz_bytes = 0;
+  int32_t sz_col = -1;
+  int64_t *d_nf = nullptr, *d_nb = nullptr, *d_fbase = nullptr, *d_bbase = nullptr;
+  void* d_scan = nullptr;
+  int64_t sz_cap = 0;
+  // staging for extracted content
+  uint8_t* d_out = nullptr; size_t d_out_cap = 0;
+  int64_t* d_fend = nullptr; size_t d_fend_cap = 0;
+};
+
+namespace b2 {
+namespace {
+
+constexpr int64_t CSV_FIELD_LIMIT = 131072;  // csv.field_size_limit() default, in code points
+
+// The header is the reader's first record whatever it holds (csv.DictReader.fieldnames), so it is
+// cut off on the host before the device scan starts: a handful of bytes, walked once.
+struct HeaderScan {
+  bool present = false;    // false: the data ended before any record did (empty file)
+  bool too_long = false;   // a name exceeds the field size limit
+  int64_t long_offset = -1;
+  int64_t data_offset = 0; // first byte after the header's line end ("\r\n" counted as one)
+};
+
+HeaderScan scan_header(const uint8_t* p, int64_t n, std::string* names, std::vector<int64_t>* ends) {
+  HeaderScan r;
+  enum { SR, SF, IF, IQ, QQ } s = SR;
+  int64_t flen = 0;
+  auto add = [&](uint8_t b, int64_t pos) {
+    if ((b & 0xc0) != 0x80) {
+      if (flen >= CSV_FIELD_LIMIT && !r.too_long) { r.too_long = true; r.long_offset = pos; }
+      ++flen;
+    }
+    names->push_back(static_cast<char>(b));
+  };
+  auto save = [&]() { ends->push_back(static_cast<int64_t>(names->size())); flen = 0; };
+  int64_t pos = 0;
+  for (; pos < n; ++pos) {
+    const uint8_t b = p[pos];
+    const bool eol = b == '\n' || b == '\r';
+    if (eol && s != IQ) {
+      if (s != SR) save();  // SR: an empty first line gives the reader's empty record: no names
+      r.present = true;
+      r.data_offset = pos + 1;
+      if (b == '\r') {
+        if (pos + 1 < n && p[pos + 1] == '\n') r.data_offset = pos + 2;
+      }
+      return r;
+    }
+    switch (s) {
+      case SR: case SF:
+        if (b == '"') s = IQ;
+        else if (b == ',') { save(); s = SF; }
+        else { add(b, pos); s = IF; }
+        break;
+      case IF:
+        if (b == ',') { save(); s = SF; }
+        else add(b, pos);
+        break;
+      case IQ:
+        if (b == '"') s = QQ;
+        else add(b, pos);
+        break;
+      case QQ:
+        if (b == '"') { add(b, pos); s = IQ; }
+        else if (b == ',') { save(); s = SF; }
+        else { add(b, pos); s = IF; }
+        break;
+    }
+  }
+  // data ended inside the header record
+  if (s != SR) { save(); r.present = true; }
+  r.data_offset = n;
+  return r;
+}
+
+int csv_size_range(b2_csv* c, int64_t start_row, int64_t n_rows, int32_t col) {
+  if (c->sz_start == start_row && c->sz_rows == n_rows && c->sz_col == col) return B2_OK;
+  b2_handle* h = c->h;
+  c->sz_start = -1;
+  if (!c->d_nf || n_rows > c->sz_cap) {
+    for (void* p : {static_cast<void*>(c->d_nf), static_cast<void*>(c->d_nb), static_cast<void*>(c->d_fbase),
+                    static_cast<void*>(c->d_bbase), c->d_scan})
+      if (p) cudaFree(p);
+    c->d_nf = c->d_nb = c->d_fbase = c->d_bbase = nullptr;
+    c->d_scan = nullptr;
+    c->sz_cap = 0;
+    const int64_t cap = n_rows + n_rows / 8 + 256;
+    B2_CUDA_OK(cudaMalloc(&c->d_nf, size_t(cap) * 8));
+    B2_CUDA_OK(cudaMalloc(&c->d_nb, size_t(cap) * 8));
+    B2_CUDA_OK(cudaMalloc(&c->d_fbase, size_t(cap + 1) * 8));
+    B2_CUDA_OK(cudaMalloc(&c->d_bbase, size_t(cap + 1) * 8));
+    B2_CUDA_OK(cudaMalloc(&c->d_scan, scan_i64_scratch_bytes(cap)));
+    c->sz_cap = cap;
+  }
+  int rc;
+  cudaStream_t st = h->stream;
+  if ((rc = csv_rows_size(st, c->d_bytes, c->row_start, c->row_end, start_row, n_rows, col, c->d_nf,
+                          c->d_nb))) return rc;
+  if ((rc = exclusive_scan_i64(st, c->d_nf, n_rows, c->d_fbase, c->d_scan))) return rc;
+  if ((rc = exclusive_scan_i64(st, c->d_nb, n_rows, c->d_bbase, c->d_scan))) return rc;
+  B2_CUDA_OK(cudaMemcpyAsync(&c->sz_fields, c->d_fbase + n_rows, 8, cudaMemcpyDeviceToHost, st));
+  B2_CUDA_OK(cudaMemcpyAsync(&c->sz_bytes, c->d_bbase + n_rows, 8, cudaMemcpyDeviceToHost, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  c->sz_start = start_row;
+  c->sz_rows = n_rows;
+  c->sz_col = col;
+  return B2_OK;
+}
+
+// content of rows [start_row, start_row + n_rows) into c->d_out / c->d_fend (device)
+int csv_extract_range(b2_csv* c, int64_t start_row, int64_t n_rows, int32_t col) {
+  int rc;
+  if ((rc = csv_size_range(c, start_row, n_rows, col))) return rc;
+  if ((rc = grow(reinterpret_cast<void**>(&c->d_out), &c->d_out_cap, size_t(c->sz_bytes) + 64))) return rc;
+  // one leading slot so that d_fend doubles as the offsets array of the tokenizer (offsets[0] = 0)
+  if ((rc = grow(reinterpret_cast<void**>(&c->d_fend), &c->d_fend_cap, size_t(c->sz_fields + 2) * 8)))
+    return rc;
+  cudaStream_t st = c->h->stream;
+  B2_CUDA_OK(cudaMemsetAsync(c->d_fend, 0, 8, st));
+  return csv_rows_write(st, c->d_bytes, c->row_start, c->row_end, start_row, n_rows, col, c->d_fbase,
+                        c->d_bbase, c->d_out, c->d_fend + 1);
+}
+
+int csv_check_range(b2_csv* c, int64_t start_row, int64_t n_rows, const char* who) {
+  if (!c) { set_last_error("%s: NULL csv", who); return B2_ERR_ARG; }
+  if (start_row < 0 || n_rows < 0 || start_row > c->rows || n_rows > c->rows - start_row) {
+    set_last_error("%s: rows [%lld, %lld) are outside the file's %lld data rows", who,
+                   static_cast<long long>(start_row), static_cast<long long>(start_row + n_rows),
+                   static_cast<long long>(c->rows));
+    return B2_ERR_ARG;
+  }
+  return B2_OK;
+}
+
+}  // namespace
+}  // namespace b2
+
+extern "C" {
+
+void b2_csv_close(b2_csv* c) {
+  if (!c) return;
+  {
+    std::lock_guard<std::mutex> lock(c->h->mu);
+    DeviceGuard guard(c->h->device);
+    for (void* p : {static_cast<void*>(c->d_bytes), static_cast<void*>(c->row_start),
+                    static_cast<void*>(c->row_end), static_cast<void*>(c->d_nf), static_cast<void*>(c->d_nb),
+                    static_cast<void*>(c->d_fbase), static_cast<void*>(c->d_bbase), c->d_scan,
+                    static_cast<void*>(c->d_out), static_cast<void*>(c->d_fend)})
+      if (p) cudaFree(p);
+  }
+  delete c;
+}
+
+int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** out, b2_csv_info* info) {
+  if (!h || !out || n_bytes < 0 || (n_bytes > 0 && !bytes)) {
+    set_last_error("b2_csv_open: NULL handle / bytes / out, or negative size");
+    return B2_ERR_ARG;
+  }
+  *out = nullptr;
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  cudaStream_t st = h->stream;
+  b2_csv* c = new b2_csv();
+  c->h = h;
+  c->n = n_bytes;
+  struct Fail {  // frees the half-built object unless released
+    b2_csv* c;
+    ~Fail() {
+      if (!c) return;
+      for (void* p : {static_cast<void*>(c->d_bytes), static_cast<void*>(c->row_start),
+                      static_cast<void*>(c->row_end)})
+        if (p) cudaFree(p);
+      delete c;
+    }
+  } fail{c};
+  void* scratch = nullptr;
+  struct FreeLater { void** p; ~FreeLater() { if (*p) cudaFree(*p); } } free_scratch{&scratch};
+
+  B2_CUDA_OK(cudaMalloc(&c->d_bytes, size_t(n_bytes) + 64));
+  B2_CUDA_OK(cudaEventRecord(h->ev_begin, st));
+  if (n_bytes) B2_CUDA_OK(cudaMemcpyAsync(c->d_bytes, bytes, n_bytes, cudaMemcpyHostToDevice, st));
+  B2_CUDA_OK(cudaMemsetAsync(c->d_bytes + n_bytes, 0, 64, st));
+
+  const HeaderScan hs = scan_header(bytes, n_bytes, &c->header_bytes, &c->header_end);
+  c->has_header = hs.present;
+  c->data_offset = hs.data_offset;
+  const int next_state = 0;  // the header's whole line end was consumed: the data starts a record
+
+  B2_CUDA_OK(cudaMalloc(&scratch, csv_index_scratch_bytes(n_bytes) + 64));
+  // results: [0] rows (i64) | [1] final state (i32) | [2] first invalid utf-8 | [3..4] field limit
+  int64_t* d_res = static_cast<int64_t*>(scratch);
+  void* d_index = static_cast<uint8_t*>(scratch) + 64;
+  int rc;
+  if ((rc = csv_count_rows(st, c->d_bytes, c->data_offset, n_bytes, next_state, d_index, d_res,
+                           reinterpret_cast<int32_t*>(d_res + 1)))) return rc;
+  if ((rc = utf8_first_invalid(st, c->d_bytes, n_bytes, reinterpret_cast<unsigned long long*>(d_res + 2))))
+    return rc;
+  int64_t res[5] = {0, 0, -1, -1, -1};
+  B2_CUDA_OK(cudaMemcpyAsync(res, d_res, 24, cudaMemcpyDeviceToHost, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  c->rows = res[0];
+  const int final_state = static_cast<int>(res[1] & 0xffffffff);
+  B2_CUDA_OK(cudaMalloc(&c->row_start, size_t(c->rows + 1) * 8));
+  B2_CUDA_OK(cudaMalloc(&c->row_end, size_t(c->rows + 1) * 8));
+  if ((rc = csv_emit_rows(st, c->d_bytes, c->data_offset, n_bytes, d_index, c->row_start, c->row_end)))
+    return rc;
+  if (c->rows > 0 && final_state > 1)  // last row has no line end
+    B2_CUDA_OK(cudaMemcpyAsync(c->row_end + c->rows - 1, &c->n, 8, cudaMemcpyHostToDevice, st));
+  if ((rc = csv_field_limit(st, c->d_bytes, c->row_start, c->row_end, c->rows, CSV_FIELD_LIMIT,
+                            reinterpret_cast<unsigned long long*>(d_res + 3)))) return rc;
+  B2_CUDA_OK(cudaMemcpyAsync(res + 3, d_res + 3, 16, cudaMemcpyDeviceToHost, st));
+  B2_CUDA_OK(cudaEventRecord(h->ev_end, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  B2_CUDA_OK(cudaEventElapsedTime(&ms, h->ev_begin, h->ev_end));
+  if (info) {
+    const int32_t want = info->struct_size;
+    b2_csv_info v{};
+    v.struct_size = sizeof(b2_csv_info);
+    v.has_header = hs.present ? 1 : 0;
+    v.header_fields = static_cast<int32_t>(c->header_end.size());
+    v.header_bytes = static_cast<int64_t>(c->header_bytes.size());
+    v.n_bytes = n_bytes;
+    v.data_offset = c->data_offset;
+    v.rows = c->rows;
+    v.first_invalid_utf8 = res[2];  // 2^64-1 reads as -1
+    v.header_field_too_long = hs.too_long ? 1 : 0;
+    v.header_long_offset = hs.long_offset;
+    v.long_field_row = res[3];
+    v.long_field_offset = res[4];
+    v.end_state = final_state;
+    v.gpu_ms = ms;
+    v.kernel_launches = 7;
+    memcpy(info, &v, std::min<size_t>(sizeof(v), want > 0 ? size_t(want) : sizeof(v)));
+  }
+  fail.c = nullptr;
+  *out = c;
+  return B2_OK;
+}
+
+int b2_csv_header(b2_csv* c, uint8_t* names, int64_t names_cap, int64_t* name_end, int32_t max_names) {
+  if (!c) { set_last_error("b2_csv_header: NULL csv"); return B2_ERR_ARG; }
+  if (names_cap < static_cast<int64_t>(c->header_bytes.size()) ||
+      max_names < static_cast<int32_t>(c->header_end.size())) {
+    set_last_error("b2_csv_header: buffers too small (need %zu bytes, %zu names)", c->header_bytes.size(),
+                   c->header_end.size());
+    return B2_ERR_LIMIT;
+  }
+  if (!c->header_bytes.empty()) memcpy(names, c->header_bytes.data(), c->header_bytes.size());
+  for (size_t i = 0; i < c->header_end.size(); ++i) name_end[i] = c->header_end[i];
+  return B2_OK;
+}
+
+int b2_csv_row_spans(b2_csv* c, int64_t start_row, int64_t n_rows, int64_t* row_start, int64_t* row_end) {
+  int rc;
+  if ((rc = csv_check_range(c, start_row, n_rows, "b2_csv_row_spans"))) return rc;
+  if (n_rows == 0) return B2_OK;
+  std::lock_guard<std::mutex> lock(c->h->mu);
+  DeviceGuard guard(c->h->device);
+  if (row_start)
+    B2_CUDA_OK(cudaMemcpy(row_start, c->row_start + start_row, size_t(n_rows) * 8, cudaMemcpyDeviceToHost));
+  if (row_end)
+    B2_CUDA_OK(cudaMemcpy(row_end, c->row_end + start_row, size_t(n_rows) * 8, cudaMemcpyDeviceToHost));
+  return B2_OK;
+}
+
+int b2_csv_rows_size(b2_csv* c, int64_t start_row, int64_t n_rows, int32_t column, int64_t* n_fields,
+                     int64_t* n_bytes) {
+  int rc;
+  if ((rc = csv_check_range(c, start_row, n_rows, "b2_csv_rows_size"))) return rc;
+  std::lock_guard<std::mutex> lock(c->h->mu);
+  DeviceGuard guard(c->h->device);
+  if ((rc = csv_size_range(c, start_row, n_rows, column))) return rc;
+  if (n_fields) *n_fields = c->sz_fields;
+  if (n_bytes) *n_bytes = c->sz_bytes;
+  return B2_OK;
+}
+
+int b2_csv_rows_read(b2_csv* c, int64_t start_row, int64_t n_rows, int32_t column, uint8_t* bytes,
+                     int64_t* field_end, int64_t* row_field_end) {
+  int rc;
+  if ((rc = csv_check_range(c, start_row, n_rows, "b2_csv_rows_read"))) return rc;
+  std::lock_guard<std::mutex> lock(c->h->mu);
+  DeviceGuard guard(c->h->device);
+  if ((rc = csv_extract_range(c, start_row, n_rows, column))) return rc;
+  cudaStream_t st = c->h->stream;
+  if (bytes && c->sz_bytes)
+    B2_CUDA_OK(cudaMemcpyAsync(bytes, c->d_out, size_t(c->sz_bytes), cudaMemcpyDeviceToHost, st));
+  if (field_end && c->sz_fields)
+    B2_CUDA_OK(cudaMemcpyAsync(field_end, c->d_fend + 1, size_t(c->sz_fields) * 8, cudaMemcpyDeviceToHost, st));
+  if (row_field_end && n_rows)
+    B2_CUDA_OK(cudaMemcpyAsync(row_field_end, c->d_fbase + 1, size_t(n_rows) * 8, cudaMemcpyDeviceToHost, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  return B2_OK;
+}
+
+int b2_csv_classify(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows, int32_t max_len,
+                    int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
+                    float* logits, b2_metrics* metrics) {
+  int rc;
+  if ((rc = csv_check_range(c, start_row, n_rows, "b2_csv_classify"))) return rc;
+  if (column < 0) { set_last_error("b2_csv_classify: column must be >= 0"); return B2_ERR_ARG; }
+  b2_handle* h = c->h;
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  if ((rc = check_len(h, max_len, true))) return rc;
+  if (!h->has_tokenizer) {
+    set_last_error("b2_csv_classify: the handle has no tokenizer");
+    return B2_ERR_ARG;
+  }
+  const int C = h->mh.num_labels;
+  if (topk < 1 || topk > C) {
+    set_last_error("topk %d is outside [1, num_labels = %d]", topk, C);
+    return B2_ERR_ARG;
+  }
+  if (n_rows > 0x7fffffff || (n_rows > 0 && (!top_idx || !top_score))) {
+    set_last_error("b2_csv_classify: too many rows or top_idx / top_score is NULL");
+    return B2_ERR_ARG;
+  }
+  if ((rc = csv_extract_range(c, start_row, n_rows, column))) return rc;
+  return classify_to_host(h, c->d_out, c->d_fend, nullptr, nullptr, n_rows, max_len, topk, top_idx,
+                          top_score, labels, histogram, logits, metrics, 0);
 }
 
 }  // extern "C"

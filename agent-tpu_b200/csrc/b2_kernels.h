@@ -97,6 +97,40 @@ int classify_head(cudaStream_t stream, const __nv_bfloat16* pooled, int ld_poole
 // token counts per sequence from the mask: lens[b] = sum(mask[b,:])
 int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B, int S);
 
+// ---- CSV (b2_csv.cu) ------------------------------------------------------------------------------
+// Record splitter with the semantics of Python's csv reader (default dialect) over bytes
+// [first, n) of a buffer that starts in `init_state` (0 = start of record, 1 = start of record
+// right after a '\r'). `scratch` needs csv_index_scratch_bytes(n) bytes and must stay untouched
+// between csv_count_rows and csv_emit_rows. `bytes` must be readable up to the next multiple of 16.
+size_t csv_index_scratch_bytes(int64_t n_bytes);
+// d_total_rows: number of non-empty records; d_final_state: automaton state after the last byte
+// (anything but 0 / 1 means the last row has no line end and ends at n).
+int csv_count_rows(cudaStream_t st, const uint8_t* bytes, int64_t first, int64_t n, int init_state,
+                   void* scratch, int64_t* d_total_rows, int32_t* d_final_state);
+// row_start[r] = offset of the first byte of row r, row_end[r] = offset of the line end closing it
+// (not written for a last row without line end).
+int csv_emit_rows(cudaStream_t st, const uint8_t* bytes, int64_t first, int64_t n, void* scratch,
+                  int64_t* row_start, int64_t* row_end);
+// *d_first_bad = first offset at which strict UTF-8 decoding fails (n: data ends inside a
+// sequence), or 2^64-1 when the bytes are valid.
+int utf8_first_invalid(cudaStream_t st, const uint8_t* bytes, int64_t n, unsigned long long* d_first_bad);
+// d_out2[0] = first row holding a field of more than `limit` code points, d_out2[1] = offset of
+// the code point that overflows it; both 2^64-1 when there is none.
+int csv_field_limit(cudaStream_t st, const uint8_t* bytes, const int64_t* row_start, const int64_t* row_end,
+                    int64_t n_rows, int64_t limit, unsigned long long* d_out2);
+// Rows [r0, r0 + n_rows): number of fields and bytes of unquoted field content per row. col >= 0
+// keeps only that column (one field per row, empty when the row is shorter).
+int csv_rows_size(cudaStream_t st, const uint8_t* bytes, const int64_t* row_start, const int64_t* row_end,
+                  int64_t r0, int64_t n_rows, int32_t col, int64_t* n_fields, int64_t* n_bytes);
+// Same walk, writing: content of row i at out_bytes + byte_base[i], end offset (in out_bytes) of its
+// field f at field_end[field_base[i] + f] (col < 0) or of its one field at field_end[i] (col >= 0).
+int csv_rows_write(cudaStream_t st, const uint8_t* bytes, const int64_t* row_start, const int64_t* row_end,
+                   int64_t r0, int64_t n_rows, int32_t col, const int64_t* field_base,
+                   const int64_t* byte_base, uint8_t* out_bytes, int64_t* field_end);
+// out[0..n] = exclusive prefix sum of in[0..n), out[n] = total. scratch: scan_i64_scratch_bytes(n).
+size_t scan_i64_scratch_bytes(int64_t n);
+int exclusive_scan_i64(cudaStream_t st, const int64_t* in, int64_t n, int64_t* out, void* scratch);
+
 // ---- weights (b2_weights.cu) -------------------------------------------------------------------
 // Deterministic synthetic initialiser shared bit-for-bit with the host generator (model_file.py):
 // value(i) = scale * (sum of four 16-bit lanes of splitmix64(seed, tensor_id, i) - 131070) + shift

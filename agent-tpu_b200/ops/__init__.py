@@ -10,8 +10,8 @@ Behaviour kept from the reference:
   * import failures are caught, printed with the `[ops]` prefix, remembered in OPS_LOAD_ERRORS and
     surface as ValueError from `get_op` (ops/__init__.py:81-84, 97-106).
 
-Only the ops of the hot path exist here: the classifier, the tokenizer and the
-plumbing `echo`. The reference's phantom entries (fibonacci, prime_factor, ... — mapped but without
+Only the ops of the hot path exist here: the classifier, the tokenizer, the CSV
+shard reader that feeds them, and the plumbing `echo`. The reference's phantom entries (fibonacci, prime_factor, ... — mapped but without
 modules) are not reproduced.
 """
 from __future__ import annotations
@@ -29,6 +29,10 @@ OP_TO_MODULE: Dict[str, str] = {
     "echo": "echo",
     "map_tokenize": "map_tokenize",
     "map_classify_tpu": "map_classify_tpu",
+    # the reference lists the module as "csv_shard" but registers the handler as "read_csv_shard",
+    # so neither name resolves there; both resolve here
+    "csv_shard": "csv_shard",
+    "read_csv_shard": "csv_shard",
 }
 
 _LOADED: Set[str] = set()

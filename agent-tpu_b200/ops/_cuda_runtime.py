@@ -84,6 +84,15 @@ class DeviceInfo(C.Structure):
                 ("cc_major", C.c_int32), ("cc_minor", C.c_int32), ("l2_bytes", C.c_int32)]
 
 
+class CsvInfo(C.Structure):
+    _fields_ = [("struct_size", C.c_int32), ("has_header", C.c_int32), ("header_fields", C.c_int32),
+                ("end_state", C.c_int32), ("header_bytes", C.c_int64), ("n_bytes", C.c_int64),
+                ("data_offset", C.c_int64), ("rows", C.c_int64), ("first_invalid_utf8", C.c_int64),
+                ("header_field_too_long", C.c_int32), ("reserved", C.c_int32),
+                ("header_long_offset", C.c_int64), ("long_field_row", C.c_int64),
+                ("long_field_offset", C.c_int64), ("gpu_ms", C.c_double), ("kernel_launches", C.c_int64)]
+
+
 def load_library():
     """dlopen libb2classify.so and declare its prototypes. Raises OSError if it is not built."""
     global _LIB
@@ -113,6 +122,17 @@ def load_library():
     lib.b2_classify_ids.argtypes = [P, P, P, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
     lib.b2_chunk_count.argtypes = [P, P, P, I64, P]
     lib.b2_chunk_bounds.argtypes = [P, P, P, I64, I64, P, I64, P]
+    lib.b2_csv_open.argtypes = [P, P, I64, C.POINTER(P), C.POINTER(CsvInfo)]
+    lib.b2_csv_close.argtypes = [P]
+    lib.b2_csv_close.restype = None
+    lib.b2_csv_header.argtypes = [P, P, I64, P, I32]
+    lib.b2_csv_row_spans.argtypes = [P, I64, I64, P, P]
+    lib.b2_csv_rows_size.argtypes = [P, I64, I64, I32, C.POINTER(I64), C.POINTER(I64)]
+    lib.b2_csv_rows_read.argtypes = [P, I64, I64, I32, P, P, P]
+    lib.b2_csv_classify.argtypes = [P, I32, I64, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
+    for name in ("b2_csv_open", "b2_csv_header", "b2_csv_row_spans", "b2_csv_rows_size", "b2_csv_rows_read",
+                 "b2_csv_classify"):
+        getattr(lib, name).restype = C.c_int
     for name in ("b2_get_device_info", "b2_create", "b2_get_model_info", "b2_set_profiling", "b2_tokenize",
                  "b2_tokenize_device", "b2_classify_text", "b2_classify_text_device", "b2_classify_ids",
                  "b2_chunk_count", "b2_chunk_bounds"):
@@ -276,6 +296,78 @@ class Engine:
         return bounds[:n_chunks]
 
 
+class CsvIndex:
+    """A CSV file resident in one engine's HBM with its record index (b2_csv_open): the device-side
+    stand-in for the `csv.DictReader` loop of _read_csv_shard (ops/csv_shard.py:9-26)."""
+
+    def __init__(self, engine: Engine, data):
+        self._lib = engine._lib
+        self._engine = engine  # keeps the handle alive
+        self._c = C.c_void_p()
+        buf = np.frombuffer(data, dtype=np.uint8) if len(data) else np.zeros(0, dtype=np.uint8)
+        self.info = CsvInfo(struct_size=C.sizeof(CsvInfo))
+        _check(self._lib, self._lib.b2_csv_open(engine.handle, _ptr(buf) if len(buf) else None, len(buf),
+                                                C.byref(self._c), C.byref(self.info)))
+        self.rows = int(self.info.rows)
+        self.n_bytes = int(self.info.n_bytes)
+
+    def close(self) -> None:
+        if getattr(self, "_c", None) is not None and self._c.value:
+            if self._engine.handle.value:  # closing the engine first frees the device context's memory
+                self._lib.b2_csv_close(self._c)
+            self._c = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def fieldnames(self) -> Optional[List[str]]:
+        """DictReader.fieldnames: None when the data holds no record at all."""
+        if not self.info.has_header:
+            return None
+        k = int(self.info.header_fields)
+        names = np.zeros(max(int(self.info.header_bytes), 1), dtype=np.uint8)
+        ends = np.zeros(max(k, 1), dtype=np.int64)
+        _check(self._lib, self._lib.b2_csv_header(self._c, _ptr(names), len(names), _ptr(ends), len(ends)))
+        raw = names.tobytes()
+        out, a = [], 0
+        for e in ends[:k].tolist():
+            out.append(raw[a:e].decode("utf-8"))
+            a = e
+        return out
+
+    def row_spans(self, start_row: int, n_rows: int) -> Tuple[np.ndarray, np.ndarray]:
+        a = np.zeros(max(n_rows, 1), dtype=np.int64)
+        e = np.zeros(max(n_rows, 1), dtype=np.int64)
+        _check(self._lib, self._lib.b2_csv_row_spans(self._c, int(start_row), int(n_rows), _ptr(a), _ptr(e)))
+        return a[:n_rows], e[:n_rows]
+
+    def rows_read(self, start_row: int, n_rows: int, column: int = -1):
+        """(content bytes, field_end[n_fields], row_field_end[n_rows]) of the unquoted fields."""
+        nf, nb = C.c_int64(0), C.c_int64(0)
+        _check(self._lib, self._lib.b2_csv_rows_size(self._c, int(start_row), int(n_rows), int(column),
+                                                     C.byref(nf), C.byref(nb)))
+        blob = np.zeros(max(nb.value, 1), dtype=np.uint8)
+        fend = np.zeros(max(nf.value, 1), dtype=np.int64)
+        rend = np.zeros(max(n_rows, 1), dtype=np.int64)
+        _check(self._lib, self._lib.b2_csv_rows_read(self._c, int(start_row), int(n_rows), int(column),
+                                                     _ptr(blob), _ptr(fend), _ptr(rend)))
+        return blob[:nb.value], fend[:nf.value], rend[:n_rows]
+
+    def classify(self, column: int, start_row: int, n_rows: int, max_len: int = 128, topk: int = 5,
+                 want_logits: bool = False) -> dict:
+        """csv -> tokenize -> classify without the text leaving the device (b2_csv_classify)."""
+        top_idx, top_score, labels, hist, logits = self._engine._outputs(n_rows, topk, want_logits)
+        m = Metrics(struct_size=C.sizeof(Metrics))
+        _check(self._lib, self._lib.b2_csv_classify(self._c, int(column), int(start_row), int(n_rows),
+                                                    int(max_len), int(topk), _ptr(top_idx), _ptr(top_score),
+                                                    _ptr(labels), _ptr(hist), _ptr(logits), C.byref(m)))
+        return {"top_idx": top_idx, "top_score": top_score, "labels": labels, "histogram": hist,
+                "logits": logits, "metrics": m.as_dict()}
+
+
 @dataclass(frozen=True)
 class CUDAHandle:
     """Counterpart of TPUHandle (ops/_tpu_runtime.py:15-20)."""
@@ -355,6 +447,8 @@ def get_cuda_handle(model_path: str, vocab_path: Optional[str] = None, max_len: 
             raise FileNotFoundError(f"CUDA tokenizer vocabulary not found: {vocab}")
 
         if _ENGINE is not None:
+            if _CSV_INDEX is not None and _CSV_INDEX._engine is _ENGINE:
+                _drop_csv_index()
             _ENGINE.close()
             _ENGINE = None
         eng = Engine(model_path, vocab, device=_local_device(), max_batch=max_batch, max_len=max_len)
@@ -385,16 +479,58 @@ def get_tokenizer_engine(vocab_path: Optional[str] = None, max_len: int = 512) -
         if vocab_path is not None and not os.path.exists(vocab_path):
             raise FileNotFoundError(f"CUDA tokenizer vocabulary not found: {vocab_path}")
         if _TOK_ENGINE is not None:
+            if _CSV_INDEX is not None and _CSV_INDEX._engine is _TOK_ENGINE:
+                _drop_csv_index()
             _TOK_ENGINE.close()
         _TOK_ENGINE = Engine(None, vocab_path, device=_local_device(), max_batch=1, max_len=max_len)
         _TOK_KEY = key
         return _TOK_ENGINE
 
 
+# The last CSV file indexed, kept resident so that successive shard tasks over one file pay for the
+# copy and the scan once (the reference re-parses from the top of the file for every shard).
+_CSV_INDEX = None
+_CSV_KEY = None
+_CSV_MAP = None
+
+
+def get_csv_index(path: str, engine: Engine):
+    """(CsvIndex, read-only mmap of the file) for `path` on `engine`; single-slot cache keyed on the
+    file's identity (real path, size, mtime) and the engine."""
+    global _CSV_INDEX, _CSV_KEY, _CSV_MAP
+    import mmap
+
+    st = os.stat(path)
+    key = (os.path.realpath(path), st.st_size, st.st_mtime_ns, id(engine), engine.handle.value)
+    with _LOCK:
+        if _CSV_INDEX is not None and _CSV_KEY == key:
+            return _CSV_INDEX, _CSV_MAP
+        _drop_csv_index()
+        with open(path, "rb") as f:
+            data = mmap.mmap(f.fileno(), 0, access=mmap.ACCESS_READ) if st.st_size > 0 else b""
+        _CSV_INDEX = CsvIndex(engine, data)
+        _CSV_MAP = data
+        _CSV_KEY = key
+        return _CSV_INDEX, _CSV_MAP
+
+
+def _drop_csv_index() -> None:
+    global _CSV_INDEX, _CSV_KEY, _CSV_MAP
+    if _CSV_INDEX is not None:
+        _CSV_INDEX.close()
+    if _CSV_MAP is not None and hasattr(_CSV_MAP, "close"):
+        try:
+            _CSV_MAP.close()
+        except BufferError:
+            pass
+    _CSV_INDEX = _CSV_KEY = _CSV_MAP = None
+
+
 def reset_cache() -> None:
     """Drop cached engines (tests)."""
     global _ENGINE, _INPUT_DETAILS, _OUTPUT_DETAILS, _MODEL_PATH, _CACHE_KEY, _TOK_ENGINE, _TOK_KEY
     with _LOCK:
+        _drop_csv_index()
         for e in (_ENGINE, _TOK_ENGINE):
             if e is not None:
                 e.close()

@@ -15,7 +15,9 @@ Added: `items: list[str]` (the key map_tokenize already uses,
 ops/map_tokenize.py:29) classifies a whole job: tokenised on the GPU, encoded in batches of
 `batch` (default 1024) at padded length `max_len` (default 128). The result then also carries
 `items_count`, `labels`, `label_histogram`, `metrics` and, with `return_results`, per-item `results`.
-Top-level `topk` stays (first item) so v0 consumers keep working.
+Top-level `topk` stays (first item) so v0 consumers keep working. `source_uri` instead of `items`
+runs the chained CSV job (see `_run_csv`): a file reference instead of a million strings in the
+payload, which the lease protocol's max_payload_bytes (app.py:108) could not carry.
 """
 from __future__ import annotations
 
@@ -50,6 +52,73 @@ def _error_envelope(payload: Dict[str, Any]) -> Dict[str, Any]:
     }
 
 
+def _run_csv(payload: Dict[str, Any], h, eng, k: int, max_len: int, t0: float) -> Dict[str, Any]:
+    """The chained job csv_shard -> map_tokenize -> map_classify in one task: `source_uri` names a CSV
+    file, `text_column` (default "text") the column holding the items, `start_row` / `shard_size`
+    the data rows to take as in read_csv_shard (ops/csv_shard.py:11-12; shard_size defaults to all
+    remaining rows). The file is indexed on the GPU and the column goes from the index to the
+    tokenizer without leaving the device; under torchrun every rank takes a contiguous slice of
+    the rows. Reading problems the reference's reader would hit raise here and so end up in this
+    op's error envelope."""
+    import os
+
+    from ._cuda_runtime import get_csv_index
+    from .csv_shard import reading_failure
+
+    source = payload["source_uri"]
+    if not isinstance(source, str) or not source:
+        raise ValueError("payload.source_uri must be a non-empty string")
+    if not os.path.exists(source):
+        raise FileNotFoundError(f"file not found: {source}")
+    start_row = int(payload.get("start_row", 0))
+    if start_row < 0:
+        raise ValueError("payload.start_row must be >= 0")
+    index, data = get_csv_index(source, eng)
+    first = min(start_row, index.rows)
+    shard_size = payload.get("shard_size")
+    count = index.rows - first if shard_size is None else min(int(shard_size), index.rows - first)
+    if count < 0 or (shard_size is not None and int(shard_size) <= 0):
+        raise ValueError("payload.shard_size must be > 0")
+    problem = reading_failure(index.info, index, data, first + count)
+    if problem:
+        raise RuntimeError(f"failed reading csv: {problem}")
+    names = index.fieldnames() or []
+    column = payload.get("text_column", "text")
+    if column not in names:
+        raise KeyError(f"column {column!r} is not in the CSV header {names}")
+    col = len(names) - 1 - names[::-1].index(column)  # DictReader keeps the last of duplicate names
+
+    lo, hi, rank, world = _shard.my_slice(count)
+    out = index.classify(col, first + lo, hi - lo, max_len=max_len, topk=k,
+                         want_logits=bool(payload.get("return_logits")))
+    metrics = dict(out["metrics"])
+    metrics["csv"] = {"bytes": index.n_bytes, "rows": index.rows, "index_gpu_ms": float(index.info.gpu_ms),
+                      "index_kernel_launches": int(index.info.kernel_launches)}
+    hist, metrics = _shard.reduce_job(out["histogram"], metrics, eng.device)
+    result = {
+        "op": OP_NAME,
+        "model_path": h.model_path,
+        "topk": _topk_dicts(out["top_idx"][0], out["top_score"][0]) if hi > lo else [],
+        "elapsed_ms": 0.0,
+        "dataset_id": payload.get("dataset_id", "unknown_dataset"),
+        "start_row": start_row,
+        "end_row": start_row + count,
+        "row_count": count,
+        "items_count": count,
+        "labels": out["labels"].tolist(),
+        "label_histogram": [int(v) for v in hist],
+        "metrics": metrics,
+    }
+    if world > 1:
+        result["shard"] = {"rank": rank, "world_size": world, "start": lo, "end": hi}
+    if payload.get("return_results"):
+        result["results"] = [{"topk": _topk_dicts(i, s)} for i, s in zip(out["top_idx"], out["top_score"])]
+    if payload.get("return_logits"):
+        result["logits"] = out["logits"].tolist()
+    result["elapsed_ms"] = (time.time() - t0) * 1000.0
+    return result
+
+
 @register_op(OP_NAME)
 def run(payload: Dict[str, Any], ctx: Dict[str, Any] = None) -> Dict[str, Any]:
     """
@@ -58,7 +127,8 @@ def run(payload: Dict[str, Any], ctx: Dict[str, Any] = None) -> Dict[str, Any]:
     Uses:
       - payload["model_path"] OR env CUDA_MODEL_PATH / TPU_MODEL_PATH OR /models/model_b200.b2m
       - payload["topk"] default 5
-      - payload["items"] (list of texts)  OR  payload["input"] (flat list[int], one row of token ids)
+      - payload["items"] (list of texts)  OR  payload["source_uri"] (CSV file, with "text_column",
+        "start_row", "shard_size")  OR  payload["input"] (flat list[int], one row of token ids)
       - payload["max_len"] default 128, payload["batch"] default 1024, payload["vocab_path"] optional
       - payload["allow_fallback"] default True
     """
@@ -108,6 +178,9 @@ def run(payload: Dict[str, Any], ctx: Dict[str, Any] = None) -> Dict[str, Any]:
                 result["logits"] = out["logits"].tolist()
             result["elapsed_ms"] = (time.time() - t0) * 1000.0
             return result
+
+        if payload.get("source_uri") is not None:
+            return _run_csv(payload, h, eng, k, max_len, t0)
 
         if "input" not in payload:
             raise ValueError('payload missing required key: "input"')

@@ -138,6 +138,67 @@ int b2_chunk_count(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, in
 int b2_chunk_bounds(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
                     int64_t chunk_size, const int64_t* chunk_base, int64_t n_chunks, int64_t* bounds);
 
+/* ---- CSV shards: read_csv_shard (ops/csv_shard.py) and the csv -> tokenize -> classify chain ----
+ *
+ * b2_csv_open copies a CSV file's bytes to the device and indexes its records once, with the
+ * semantics of the reference's reader: csv.DictReader over open(path, newline="", encoding="utf-8")
+ * (ops/csv_shard.py:17-18) — default dialect, the first record is the header, records without any
+ * field (blank lines) are dropped, quoted fields may hold commas, quotes ("" -> ") and line ends.
+ * Shards are then cut from the index instead of re-parsing the file from the top as
+ * _read_csv_shard does (ops/csv_shard.py:19-24). Rows are 0-based over data rows, as `start_row`
+ * is in the reference (ops/csv_shard.py:11-12). */
+typedef struct b2_csv b2_csv;
+typedef struct b2_csv_info {
+  int32_t struct_size;    /* sizeof(b2_csv_info), set by the caller */
+  int32_t has_header;     /* 0: the data held no record at all (DictReader.fieldnames is None) */
+  int32_t header_fields;  /* number of header names (0 for a blank first line) */
+  int32_t end_state;      /* automaton state after the last byte; > 1: last row has no line end */
+  int64_t header_bytes;   /* bytes of the unquoted header names, see b2_csv_header */
+  int64_t n_bytes;
+  int64_t data_offset;    /* offset of the first byte after the header record */
+  int64_t rows;           /* data rows: what DictReader yields over the whole file */
+  /* What the reference would trip over while reading (it reports them as
+   * "failed reading csv: ..." only if it reads that far: ops/csv_shard.py:78-81): */
+  int64_t first_invalid_utf8;    /* offset where strict UTF-8 decoding fails, n_bytes if the data
+                                    ends inside a sequence, -1 if the bytes are valid */
+  int32_t header_field_too_long; /* 1: a header name exceeds csv.field_size_limit() = 131072 */
+  int32_t reserved;
+  int64_t header_long_offset;    /* offset of the code point that overflows it, else -1 */
+  int64_t long_field_row;        /* first data row with a field above the limit, else -1 */
+  int64_t long_field_offset;     /* offset of the code point that overflows it, else -1 */
+  double gpu_ms;                 /* copy + index, CUDA events on the handle's stream */
+  int64_t kernel_launches;
+} b2_csv_info;
+
+/* bytes: the whole file in host memory (n_bytes may be 0). The csv object belongs to handle h, uses
+ * its device and stream, and must be closed before the handle is destroyed. */
+int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** out, b2_csv_info* info);
+void b2_csv_close(b2_csv* c);
+/* Header names, unquoted, back to back in names[0 .. info.header_bytes); name i ends at
+ * name_end[i]. Replaces DictReader.fieldnames. */
+int b2_csv_header(b2_csv* c, uint8_t* names, int64_t names_cap, int64_t* name_end, int32_t max_names);
+/* Byte offsets in the file of rows [start_row, start_row + n_rows): first byte, and the line end
+ * that closes the row (n_bytes for a last row without one). Either pointer may be NULL. */
+int b2_csv_row_spans(b2_csv* c, int64_t start_row, int64_t n_rows, int64_t* row_start, int64_t* row_end);
+/* Size the content of rows [start_row, start_row + n_rows): total number of fields and total bytes
+ * of unquoted field content. column >= 0 keeps only that column: one field per row, empty where
+ * the row is shorter; column < 0 keeps every field. */
+int b2_csv_rows_size(b2_csv* c, int64_t start_row, int64_t n_rows, int32_t column, int64_t* n_fields,
+                     int64_t* n_bytes);
+/* Fetch what b2_csv_rows_size sized: field content back to back in bytes, field j ends at
+ * field_end[j], row i's last field is field row_field_end[i] - 1 (rows in order, so row i holds
+ * fields [row_field_end[i-1], row_field_end[i])). Replaces the `rows.append(row)` loop of
+ * _read_csv_shard (ops/csv_shard.py:19-24); building the dicts stays with the caller. */
+int b2_csv_rows_read(b2_csv* c, int64_t start_row, int64_t n_rows, int32_t column, uint8_t* bytes,
+                     int64_t* field_end, int64_t* row_field_end);
+/* The chained job of BASELINE config 5: take `column` of rows [start_row, start_row + n_rows) as
+ * the text items and classify them like b2_classify_text — the extracted text never leaves the
+ * device. No reference counterpart (the agent runs one op per task: app.py:283-287); outputs as
+ * in b2_classify_text, host pointers. */
+int b2_csv_classify(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows, int32_t max_len,
+                    int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
+                    float* logits, b2_metrics* metrics);
+
 /* Tokenize-and-pad like b2_tokenize, but without allocating device memory during the call.
  * No counterpart in the reference. It exists for callers that are not allowed to ask the CUDA
  * driver for memory once they are running (a worker with a fixed memory budget, a loop that cannot
