@@ -1309,6 +1309,10 @@ int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** ou
   const int next_state = 0;  // the header's whole line end was consumed: the data starts a record
 
   B2_CUDA_OK(cudaMalloc(&scratch, csv_index_scratch_bytes(n_bytes) + 64));
+  cudaEvent_t ev_copied = nullptr;
+  B2_CUDA_OK(cudaEventCreate(&ev_copied));
+  struct DropEvent { cudaEvent_t e; ~DropEvent() { cudaEventDestroy(e); } } drop_event{ev_copied};
+  B2_CUDA_OK(cudaEventRecord(ev_copied, st));
   // results: [0] rows (i64) | [1] final state (i32) | [2] first invalid utf-8 | [3..4] field limit
   int64_t* d_res = static_cast<int64_t*>(scratch);
   void* d_index = static_cast<uint8_t*>(scratch) + 64;
@@ -1333,8 +1337,9 @@ int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** ou
   B2_CUDA_OK(cudaMemcpyAsync(res + 3, d_res + 3, 16, cudaMemcpyDeviceToHost, st));
   B2_CUDA_OK(cudaEventRecord(h->ev_end, st));
   B2_CUDA_OK(cudaStreamSynchronize(st));
-  float ms = 0.f;
+  float ms = 0.f, index_ms = 0.f;
   B2_CUDA_OK(cudaEventElapsedTime(&ms, h->ev_begin, h->ev_end));
+  B2_CUDA_OK(cudaEventElapsedTime(&index_ms, ev_copied, h->ev_end));
   if (info) {
     const int32_t want = info->struct_size;
     b2_csv_info v{};
@@ -1352,6 +1357,7 @@ int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** ou
     v.long_field_offset = res[4];
     v.end_state = final_state;
     v.gpu_ms = ms;
+    v.index_ms = index_ms;
     v.kernel_launches = 7;
     memcpy(info, &v, std::min<size_t>(sizeof(v), want > 0 ? size_t(want) : sizeof(v)));
   }

@@ -90,7 +90,8 @@ class CsvInfo(C.Structure):
                 ("data_offset", C.c_int64), ("rows", C.c_int64), ("first_invalid_utf8", C.c_int64),
                 ("header_field_too_long", C.c_int32), ("reserved", C.c_int32),
                 ("header_long_offset", C.c_int64), ("long_field_row", C.c_int64),
-                ("long_field_offset", C.c_int64), ("gpu_ms", C.c_double), ("kernel_launches", C.c_int64)]
+                ("long_field_offset", C.c_int64), ("gpu_ms", C.c_double), ("kernel_launches", C.c_int64),
+                ("index_ms", C.c_double)]
 
 
 def load_library():

@@ -168,6 +168,7 @@ typedef struct b2_csv_info {
   int64_t long_field_offset;     /* offset of the code point that overflows it, else -1 */
   double gpu_ms;                 /* copy + index, CUDA events on the handle's stream */
   int64_t kernel_launches;
+  double index_ms;               /* the index kernels alone (after the copy), incl. two tiny readbacks */
 } b2_csv_info;
 
 /* bytes: the whole file in host memory (n_bytes may be 0). The csv object belongs to handle h, uses
