@@ -1306,9 +1306,8 @@ int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** ou
   const HeaderScan hs = scan_header(bytes, n_bytes, &c->header_bytes, &c->header_end);
   c->has_header = hs.present;
   c->data_offset = hs.data_offset;
-  const int next_state = 0;  // the header's whole line end was consumed: the data starts a record
 
-  B2_CUDA_OK(cudaMalloc(&scratch, csv_index_scratch_bytes(n_bytes) + 64));
+  B2_CUDA_OK(cudaMallocAsync(&scratch, csv_index_scratch_bytes(n_bytes) + 64, st));  // stream-ordered: no device-wide stall
   cudaEvent_t ev_copied = nullptr;
   B2_CUDA_OK(cudaEventCreate(&ev_copied));
   struct DropEvent { cudaEvent_t e; ~DropEvent() { cudaEventDestroy(e); } } drop_event{ev_copied};
@@ -1317,20 +1316,19 @@ int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** ou
   int64_t* d_res = static_cast<int64_t*>(scratch);
   void* d_index = static_cast<uint8_t*>(scratch) + 64;
   int rc;
-  if ((rc = csv_count_rows(st, c->d_bytes, c->data_offset, n_bytes, next_state, d_index, d_res,
-                           reinterpret_cast<int32_t*>(d_res + 1)))) return rc;
-  if ((rc = utf8_first_invalid(st, c->d_bytes, n_bytes, reinterpret_cast<unsigned long long*>(d_res + 2))))
-    return rc;
+  if ((rc = csv_count_rows(st, c->d_bytes, c->data_offset, n_bytes, d_index, d_res,
+                           reinterpret_cast<int32_t*>(d_res + 1),
+                           reinterpret_cast<unsigned long long*>(d_res + 2)))) return rc;
   int64_t res[5] = {0, 0, -1, -1, -1};
   B2_CUDA_OK(cudaMemcpyAsync(res, d_res, 24, cudaMemcpyDeviceToHost, st));
   B2_CUDA_OK(cudaStreamSynchronize(st));
   c->rows = res[0];
   const int final_state = static_cast<int>(res[1] & 0xffffffff);
-  B2_CUDA_OK(cudaMalloc(&c->row_start, size_t(c->rows + 1) * 8));
-  B2_CUDA_OK(cudaMalloc(&c->row_end, size_t(c->rows + 1) * 8));
-  if ((rc = csv_emit_rows(st, c->d_bytes, c->data_offset, n_bytes, d_index, c->row_start, c->row_end)))
+  B2_CUDA_OK(cudaMallocAsync(&c->row_start, size_t(c->rows + 1) * 8, st));
+  B2_CUDA_OK(cudaMallocAsync(&c->row_end, size_t(c->rows + 1) * 8, st));
+  if ((rc = csv_emit_rows(st, c->data_offset, n_bytes, d_index, c->row_start, c->row_end)))
     return rc;
-  if (c->rows > 0 && final_state > 1)  // last row has no line end
+  if (c->rows > 0 && final_state != 0)  // last row has no line end
     B2_CUDA_OK(cudaMemcpyAsync(c->row_end + c->rows - 1, &c->n, 8, cudaMemcpyHostToDevice, st));
   if ((rc = csv_field_limit(st, c->d_bytes, c->row_start, c->row_end, c->rows, CSV_FIELD_LIMIT,
                             reinterpret_cast<unsigned long long*>(d_res + 3)))) return rc;
@@ -1358,7 +1356,7 @@ int b2_csv_open(b2_handle* h, const uint8_t* bytes, int64_t n_bytes, b2_csv** ou
     v.end_state = final_state;
     v.gpu_ms = ms;
     v.index_ms = index_ms;
-    v.kernel_launches = 7;
+    v.kernel_launches = 6;
     memcpy(info, &v, std::min<size_t>(sizeof(v), want > 0 ? size_t(want) : sizeof(v)));
   }
   fail.c = nullptr;

@@ -99,21 +99,19 @@ int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B,
 
 // ---- CSV (b2_csv.cu) ------------------------------------------------------------------------------
 // Record splitter with the semantics of Python's csv reader (default dialect) over bytes
-// [first, n) of a buffer that starts in `init_state` (0 = start of record, 1 = start of record
-// right after a '\r'). `scratch` needs csv_index_scratch_bytes(n) bytes and must stay untouched
-// between csv_count_rows and csv_emit_rows. `bytes` must be readable up to the next multiple of 16.
+// [first, n) of a buffer; the data starts a record at `first`. `scratch` needs
+// csv_index_scratch_bytes(n) bytes and must stay untouched between csv_count_rows and
+// csv_emit_rows. `bytes` must be readable up to the next multiple of 16.
 size_t csv_index_scratch_bytes(int64_t n_bytes);
 // d_total_rows: number of non-empty records; d_final_state: automaton state after the last byte
-// (anything but 0 / 1 means the last row has no line end and ends at n).
-int csv_count_rows(cudaStream_t st, const uint8_t* bytes, int64_t first, int64_t n, int init_state,
-                   void* scratch, int64_t* d_total_rows, int32_t* d_final_state);
+// (anything but 0 means the last row has no line end and ends at n); *d_first_bad = first offset in
+// [0, n) at which strict UTF-8 decoding fails (n: data ends inside a sequence), 2^64-1 if valid.
+int csv_count_rows(cudaStream_t st, const uint8_t* bytes, int64_t first, int64_t n, void* scratch,
+                   int64_t* d_total_rows, int32_t* d_final_state, unsigned long long* d_first_bad);
 // row_start[r] = offset of the first byte of row r, row_end[r] = offset of the line end closing it
 // (not written for a last row without line end).
-int csv_emit_rows(cudaStream_t st, const uint8_t* bytes, int64_t first, int64_t n, void* scratch,
-                  int64_t* row_start, int64_t* row_end);
-// *d_first_bad = first offset at which strict UTF-8 decoding fails (n: data ends inside a
-// sequence), or 2^64-1 when the bytes are valid.
-int utf8_first_invalid(cudaStream_t st, const uint8_t* bytes, int64_t n, unsigned long long* d_first_bad);
+int csv_emit_rows(cudaStream_t st, int64_t first, int64_t n, void* scratch, int64_t* row_start,
+                  int64_t* row_end);
 // d_out2[0] = first row holding a field of more than `limit` code points, d_out2[1] = offset of
 // the code point that overflows it; both 2^64-1 when there is none.
 int csv_field_limit(cudaStream_t st, const uint8_t* bytes, const int64_t* row_start, const int64_t* row_end,
