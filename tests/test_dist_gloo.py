@@ -51,3 +51,71 @@ def test_two_rank_histogram_allreduce():
     for m in (m0, m1):
         assert m["items"] == 1001 and m["tokens"] == 10010 and m["kernel_launches"] == 180
         assert m["gpu_ms_total"] == 6.0 and m["world_size"] == 2
+
+
+def _chain_worker(rank, world, port, q, path):
+    """The CSV chain op on two ranks, with the GPU replaced by a stand-in built on the oracle's index:
+    what is under test is the slicing of the requested rows and the reduce of the histogram."""
+    sys.path.insert(0, os.path.join(ROOT, "agent-tpu_b200"))
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import types
+
+    import torch.distributed as dist
+    import csv_oracle
+    from ops import _cuda_runtime as rt, map_classify_tpu as op
+
+    C = 4
+    data = open(path, "rb").read()
+
+    class FakeIndex(csv_oracle.OracleIndex):
+        def classify(self, column, start_row, n_rows, max_len=128, topk=5, want_logits=False):
+            blob, fend, _ = self.rows_read(start_row, n_rows, column)
+            lens = np.diff(np.concatenate([[0], fend]))
+            labels = (lens % C).astype(np.int32)
+            top_idx = np.tile(np.arange(topk, dtype=np.int32), (n_rows, 1))
+            return {"top_idx": top_idx, "top_score": np.full((n_rows, topk), 0.25, np.float32), "labels": labels,
+                    "histogram": np.bincount(labels, minlength=C).astype(np.int64), "logits": None,
+                    "metrics": {"items": n_rows, "tokens": int(lens.sum()), "padded_tokens": 128 * n_rows,
+                                "batches": 1, "kernel_launches": 92, "h2d_bytes": 0, "d2h_bytes": 0,
+                                "gpu_ms_total": 1.0 + rank}}
+
+    fake_index = FakeIndex(data)
+    fake_index.info.gpu_ms = 0.5
+    fake_index.info.kernel_launches = 6
+    engine = types.SimpleNamespace(device=0)
+    handle = types.SimpleNamespace(interpreter=engine, output_details=[{"shape": (1, C)}], model_path="fake.b2m")
+    op.get_cuda_handle = lambda *a, **k: handle
+    rt.get_csv_index = lambda path, eng: (fake_index, data)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        res = op.run({"source_uri": path, "start_row": 3, "shard_size": 101, "topk": 2, "allow_fallback": False})
+        q.put((rank, res["shard"], res["labels"], res["label_histogram"], res["row_count"], res["end_row"],
+               res["metrics"]["items"], res["metrics"]["world_size"]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_csv_chain(tmp_path):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from csv_cases import _table
+    path = os.path.join(str(tmp_path), "chain.csv")
+    with open(path, "wb") as f:
+        f.write(_table(150, 9))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_chain_worker, args=(r, 2, port, q, path)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, s0, l0, h0, n0, e0, i0, w0), (_, s1, l1, h1, n1, e1, i1, w1) = got
+    assert (s0["start"], s0["end"], s1["start"], s1["end"]) == (0, 50, 50, 101)
+    assert n0 == n1 == 101 and e0 == e1 == 104 and i0 == i1 == 101 and w0 == w1 == 2
+    assert h0 == h1 == np.bincount(np.array(l0 + l1), minlength=4).tolist()
+    # the two slices together are the text column of rows [3, 104) in order
+    import csv as pycsv, io
+    rows = list(pycsv.DictReader(io.StringIO(open(path, "rb").read().decode(), newline="")))[3:104]
+    assert l0 + l1 == [len(r["text"].encode()) % 4 for r in rows]
