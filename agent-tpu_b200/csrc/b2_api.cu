@@ -141,7 +141,7 @@ struct b2_handle {
   // LayerNorm folding (B2_NO_LN_FOLD=1 turns it off): no LayerNorm kernel runs in the encoder; the
   // un-normalised sums stay in x / y and (mean, rstd) per row travel in stats_a / stats_b
   bool fold_ln = true;
-  float2 *stats_a = nullptr, *stats_b = nullptr, *part = nullptr;
+  float2 *stats_a = nullptr, *stats_b = nullptr, *part = nullptr, *part_b = nullptr;
   float *ones = nullptr, *zeros = nullptr;
   int part_slots = 0;
   int32_t* cu = nullptr;
@@ -150,6 +150,10 @@ struct b2_handle {
   __nv_bfloat16 *cls = nullptr, *cls_ctx = nullptr, *cls_y = nullptr, *cls_f = nullptr;
   CUtensorMap tm_cls{}, tm_cls_ctx{}, tm_cls_y{}, tm_cls_f{};
 
+  // token ids / lengths of a run of items of the job: the tokenizer runs once per TOKENIZE_RUN items
+  // (one launch fills the GPU; one launch per 1,024-item batch leaves most of it idle)
+  int32_t* job_ids = nullptr; size_t job_ids_cap = 0;
+  int32_t* job_lens = nullptr; size_t job_lens_cap = 0;
   // growable staging for host-pointer calls
   uint8_t* st_text = nullptr; size_t st_text_cap = 0;
   int64_t* st_off = nullptr; size_t st_off_cap = 0;
@@ -382,10 +386,12 @@ int alloc_activations(b2_handle* h) {
   if ((rc = A(reinterpret_cast<void**>(&h->stats_a), rows * 8))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->stats_b), rows * 8))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->part), rows * h->part_slots * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->part_b), rows * h->part_slots * 8))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->ones), H * 4))) return rc;
   if ((rc = A(reinterpret_cast<void**>(&h->zeros), H * 4))) return rc;
   B2_CUDA_OK(cudaMemsetAsync(h->zeros, 0, H * 4, h->stream));
   B2_CUDA_OK(cudaMemsetAsync(h->part, 0, rows * h->part_slots * 8, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(h->part_b, 0, rows * h->part_slots * 8, h->stream));
   if ((rc = fill_synthetic_f32(h->stream, h->ones, H, 0, 0, 0.0f, 1.0f))) return rc;  // 0*x + 1
   if ((rc = A(reinterpret_cast<void**>(&h->cls), int64_t(h->max_batch) * H * 2))) return rc;
   B2_CUDA_OK(cudaMemsetAsync(h->cls, 0, int64_t(h->max_batch) * H * 2, h->stream));
@@ -416,6 +422,8 @@ int alloc_activations(b2_handle* h) {
   return B2_OK;
 }
 
+constexpr int64_t TOKENIZE_RUN = 32768;  // items per tokenizer launch inside a job
+
 __global__ void sum_lens_kernel(const int32_t* lens, int n, int64_t* total) {
   long long s = 0;
   for (int i = threadIdx.x; i < n; i += blockDim.x) s += lens[i];
@@ -435,9 +443,10 @@ __global__ void hist_to_i64_kernel(const unsigned long long* src, int64_t* dst, 
   if (i < n) dst[i] = static_cast<int64_t>(src[i]);
 }
 
-// Encoder + head for one batch whose ids / lens are already in h->ids / h->lens.
-int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, float* d_top_score,
-                  int32_t* d_labels, float* d_logits, int64_t* launches) {
+// Encoder + head for one batch: ids [B, S] and lens [B] in device memory.
+int forward_batch(b2_handle* h, const int32_t* ids, const int32_t* lens, int B, int S, int topk,
+                  int32_t* d_top_idx, float* d_top_score, int32_t* d_labels, float* d_logits,
+                  int64_t* launches) {
   const ModelHeader& m = h->mh;
   const int H = m.hidden, I = m.intermediate, M = B * S;
   cudaStream_t st = h->stream;
@@ -447,11 +456,11 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
   const int32_t* m_dev = h->packed ? h->cu + B : nullptr;
   mark(h, K_EMBED);
   if (h->packed) {
-    if ((rc = pack_offsets(st, h->lens, B, h->cu))) return rc;
+    if ((rc = pack_offsets(st, lens, B, h->cu))) return rc;
     ++*launches;
   }
-  if ((rc = embed_layernorm(st, h->ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, h->x,
-                            M, S, H, m.vocab_size, h->packed ? h->lens : nullptr, cu))) return rc;
+  if ((rc = embed_layernorm(st, ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, h->x,
+                            M, S, H, m.vocab_size, h->packed ? lens : nullptr, cu))) return rc;
   ++*launches;
   // encoder projections: CTA-pair kernel when the batch is large enough to fill 74 pairs
   const bool pair = h->pair_gemm && M >= 4096;
@@ -464,7 +473,12 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
   const bool fold = h->fold_ln;
   // folded path: x / y hold un-normalised sums; the LayerNorm that turns them into layer inputs is
   // described by (stats, gamma, beta) and applied inside the consuming GEMMs' epilogues
+  // Row statistics reach the consuming epilogues as the 12 partial (Σ, Σ²) slots the producing GEMM
+  // wrote (in_part; summed in slot order by every reader) — except for the embedding output, which
+  // is already normalised (identity statistics in stats_b).
   const float2* in_stats = h->stats_b;
+  const float2* in_part = nullptr;
+  const float inv_h = 1.0f / static_cast<float>(H);
   const float* in_g = h->ones;
   const float* in_b = h->zeros;
   if (fold) {
@@ -480,7 +494,7 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
     mark(h, K_GEMM_QKV);
     if (fold) {
       GemmLnArgs a;
-      a.row_stats = in_stats;
+      a.row_stats = in_stats; a.part_in = in_part; a.part_slots = h->part_slots; a.inv_h = inv_h; a.eps = m.ln_eps;
       a.g = L.g_qkv;
       if ((rc = gemm_ln(h->tm_x, L.tm2_qkv_f, h->tm_qkv_c, L.c_qkv, nullptr, 3 * H, H, GEMM_EPI_LNIN, a)))
         return rc;
@@ -489,13 +503,18 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
       return rc;
     }
     mark(h, K_ATTENTION);
-    if ((rc = attention_bf16(st, h->tm_att, h->ctx, h->lens, B, S, H, cu))) return rc;
+    if ((rc = attention_bf16(st, h->tm_att, h->ctx, lens, B, S, H, cu))) return rc;
     if (l + 1 == m.layers) {
       // last layer: only the [CLS] rows are read downstream (pooler), and every remaining kernel is
       // row-wise, so run them on the B gathered rows; per-row results are unchanged
       mark(h, K_GEMM_OUT);
       if ((rc = gather_cls_rows(st, h->ctx, cu, S, B, H, h->cls_ctx))) return rc;
       if (fold) {
+        if (in_part) {  // the gather wants finished (mean, rstd): one finalize per batch, not one per GEMM
+          if ((rc = ln_stats_finalize(st, in_part, h->part_slots, M, H, m.ln_eps, h->stats_a, m_dev))) return rc;
+          in_stats = h->stats_a;
+          ++*launches;
+        }
         if ((rc = gather_cls_rows_norm(st, h->x, in_stats, in_g, in_b, cu, S, B, H, h->cls))) return rc;
       } else if ((rc = gather_cls_rows(st, h->x, cu, S, B, H, h->cls))) {
         return rc;
@@ -518,25 +537,29 @@ int forward_batch(b2_handle* h, int B, int S, int topk, int32_t* d_top_idx, floa
     if (fold) {
       GemmLnArgs a;
       mark(h, K_GEMM_OUT);
-      a.row_stats = in_stats; a.res_gamma = in_g; a.res_beta = in_b;
-      a.part_out = h->part; a.part_slots = h->part_slots;
+      a.row_stats = in_stats; a.part_in = in_part; a.inv_h = inv_h; a.eps = m.ln_eps;
+      a.res_gamma = in_g; a.res_beta = in_b;
+      a.part_out = h->part; a.part_slots = h->part_slots;  // statistics of y
       if ((rc = gemm_ln(h->tm_ctx, L.tm2_o, h->tm_y, L.bo, &h->tm_x, H, H, GEMM_EPI_LNRES_STATS, a))) return rc;
+      // y's statistics feed the two widest epilogues (FFN1 has 12 column tiles per row block, each
+      // of which would re-add the 12 slots): finish them once; x's statistics (below) are read as
+      // partials by QKV and the out-projection, which saves the second finalize of the layer
       mark(h, K_LAYERNORM);
       if ((rc = ln_stats_finalize(st, h->part, h->part_slots, M, H, m.ln_eps, h->stats_a, m_dev))) return rc;
       mark(h, K_GEMM_FFN1);
       GemmLnArgs f1;
-      f1.row_stats = h->stats_a; f1.g = L.g_1;
+      f1.row_stats = h->stats_a;
+      f1.g = L.g_1;
       if ((rc = gemm_ln(h->tm_y, L.tm2_1_f, h->tm_ffn, L.c_1, nullptr, I, H, GEMM_EPI_LNIN_GELU, f1)))
         return rc;
       mark(h, K_GEMM_FFN2);
       GemmLnArgs f2;
-      f2.row_stats = h->stats_a; f2.res_gamma = L.ln1_g; f2.res_beta = L.ln1_b;
-      f2.part_out = h->part; f2.part_slots = h->part_slots;
+      f2.row_stats = h->stats_a;
+      f2.res_gamma = L.ln1_g; f2.res_beta = L.ln1_b;
+      f2.part_out = h->part_b; f2.part_slots = h->part_slots;  // statistics of the next layer's x
       if ((rc = gemm_ln(h->tm_ffn, L.tm2_2, h->tm_x, L.b2, &h->tm_y, H, I, GEMM_EPI_LNRES_STATS, f2))) return rc;
-      mark(h, K_LAYERNORM);
-      if ((rc = ln_stats_finalize(st, h->part, h->part_slots, M, H, m.ln_eps, h->stats_b, m_dev))) return rc;
-      in_stats = h->stats_b; in_g = L.ln2_g; in_b = L.ln2_b;
-      *launches += 7;
+      in_part = h->part_b; in_g = L.ln2_g; in_b = L.ln2_b;
+      *launches += 6;
       continue;
     }
     mark(h, K_GEMM_OUT);
@@ -644,25 +667,41 @@ int classify_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offset
   B2_CUDA_OK(cudaMemsetAsync(h->d_tokens, 0, 8, st));
   B2_CUDA_OK(cudaEventRecord(h->ev_begin, st));
   int64_t batches = 0;
+  // Text is tokenised TOKENIZE_RUN items at a time, ahead of the batches that consume it.
+  const int64_t run_items = std::max<int64_t>(h->max_batch, TOKENIZE_RUN / h->max_batch * h->max_batch);
+  if (d_utf8 && n > 0) {
+    const int64_t cap = std::min<int64_t>(n, run_items);
+    if ((rc = grow(reinterpret_cast<void**>(&h->job_ids), &h->job_ids_cap, size_t(cap) * max_len * 4)))
+      return rc;
+    if ((rc = grow(reinterpret_cast<void**>(&h->job_lens), &h->job_lens_cap, size_t(cap) * 4))) return rc;
+  }
+  int64_t run0 = 0;  // first item of the current tokenizer run
   // labels are needed for the histogram even when the caller does not want them
   for (int64_t i0 = 0; i0 < n; i0 += h->max_batch) {
     const int B = static_cast<int>(std::min<int64_t>(h->max_batch, n - i0));
+    const int32_t *ids = h->ids, *lens = h->lens;
     if (d_utf8) {
-      mark(h, K_TOKENIZE);
-      if ((rc = tokenizer_run(st, h->tok, d_utf8, d_offsets + i0, B, max_len, h->ids, nullptr, h->lens,
-                              h->num_sms))) return rc;
-      acc.launches += 1;
+      if (i0 == 0 || i0 >= run0 + run_items) {
+        run0 = i0;
+        const int run_n = static_cast<int>(std::min<int64_t>(run_items, n - run0));
+        mark(h, K_TOKENIZE);
+        if ((rc = tokenizer_run(st, h->tok, d_utf8, d_offsets + run0, run_n, max_len, h->job_ids, nullptr,
+                                h->job_lens, h->num_sms))) return rc;
+        sum_lens_kernel<<<1, 1024, 0, st>>>(h->job_lens, run_n, h->d_tokens);
+        acc.launches += 2;
+      }
+      ids = h->job_ids + (i0 - run0) * max_len;
+      lens = h->job_lens + (i0 - run0);
     } else {
       B2_CUDA_OK(cudaMemcpyAsync(h->ids, d_ids_in + i0 * max_len, size_t(B) * max_len * 4,
                                  cudaMemcpyDeviceToDevice, st));
       if ((rc = mask_to_lens(st, d_mask_in + i0 * max_len, h->lens, B, max_len))) return rc;
-      acc.launches += 1;
+      sum_lens_kernel<<<1, 256, 0, st>>>(h->lens, B, h->d_tokens);
+      acc.launches += 2;
     }
-    sum_lens_kernel<<<1, 256, 0, st>>>(h->lens, B, h->d_tokens);
-    acc.launches += 1;
     int32_t* lab = d_labels ? d_labels + i0 : reinterpret_cast<int32_t*>(h->mask);  // scratch
-    if ((rc = forward_batch(h, B, max_len, topk, d_top_idx + i0 * topk, d_top_score + i0 * topk, lab,
-                            d_logits ? d_logits + i0 * C : nullptr, &acc.launches))) return rc;
+    if ((rc = forward_batch(h, ids, lens, B, max_len, topk, d_top_idx + i0 * topk, d_top_score + i0 * topk,
+                            lab, d_logits ? d_logits + i0 * C : nullptr, &acc.launches))) return rc;
     if ((rc = flush_profile(h, &acc))) return rc;
     ++batches;
   }
@@ -803,6 +842,8 @@ void b2_destroy(b2_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   for (void* p : h->allocations) cudaFree(p);
   if (h->has_tokenizer) tokenizer_free(&h->tok);
+  if (h->job_ids) cudaFree(h->job_ids);
+  if (h->job_lens) cudaFree(h->job_lens);
   if (h->st_text) cudaFree(h->st_text);
   if (h->st_off) cudaFree(h->st_off);
   if (h->st_out) cudaFree(h->st_out);

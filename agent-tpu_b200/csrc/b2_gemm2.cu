@@ -251,7 +251,31 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
         tma_load_2d(buf, &tmap_r, rfull_bar(quarter), colq, row_base);
       }
       float2 st = make_float2(0.f, 1.f);  // (mean, rstd) of this row
-      if (kLnIn || kLnRes) st = row_ok ? __ldg(ln.row_stats + row) : st;
+      if ((kLnIn || kLnRes) && row_ok) {
+        if (ln.part_in) {
+          // hidden is a multiple of 128, so a row holds an even number (<= 16) of 8-byte slots: fetch
+          // them as float4 pairs, all loads in flight together, then add in slot order (every reader
+          // gets the same bits)
+          const float4* pp = reinterpret_cast<const float4*>(ln.part_in + static_cast<size_t>(row) * ln.part_slots);
+          const int pairs = ln.part_slots >> 1;
+          float4 pv[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) pv[i] = i < pairs ? __ldg(pp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          float s = 0.f, sq = 0.f;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (i < pairs) {
+              s += pv[i].x; sq += pv[i].y;
+              s += pv[i].z; sq += pv[i].w;
+            }
+          }
+          const float mean = s * ln.inv_h;
+          const float var = fmaxf(sq * ln.inv_h - mean * mean, 0.f);
+          st = make_float2(mean, rsqrtf(var + ln.eps));
+        } else {
+          st = __ldg(ln.row_stats + row);
+        }
+      }
       float psum = 0.f, psq = 0.f;
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
@@ -420,7 +444,11 @@ int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap&
       return launch2<GEMM_EPI_BIAS_TANH>(stream, ta, tb, tc, trr, bias, M, N, K, num_sms, m_dev, ln);
     case GEMM_EPI_LNIN:
     case GEMM_EPI_LNIN_GELU:
-      if (!ln.row_stats || !ln.g) {
+      if (ln.part_in && (ln.part_slots < 2 || ln.part_slots > 16 || (ln.part_slots & 1))) {
+        set_last_error("gemm2_bf16_tn: part_in needs an even number of slots in [2, 16]");
+        return B2_ERR_ARG;
+      }
+      if ((!ln.row_stats && !ln.part_in) || !ln.g) {
         set_last_error("gemm2_bf16_tn: LNIN epilogue needs row_stats and g");
         return B2_ERR_ARG;
       }
@@ -428,7 +456,7 @@ int gemm2_bf16_tn(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap&
                  ? launch2<GEMM_EPI_LNIN>(stream, ta, tb, tc, trr, bias, M, N, K, num_sms, m_dev, ln)
                  : launch2<GEMM_EPI_LNIN_GELU>(stream, ta, tb, tc, trr, bias, M, N, K, num_sms, m_dev, ln);
     case GEMM_EPI_LNRES_STATS:
-      if (!ln.row_stats || !ln.res_gamma || !ln.res_beta || !ln.part_out || ln.part_slots * 64 < N) {
+      if ((!ln.row_stats && !ln.part_in) || !ln.res_gamma || !ln.res_beta || !ln.part_out || ln.part_slots * 64 < N) {
         set_last_error("gemm2_bf16_tn: LNRES_STATS epilogue needs row_stats, gamma, beta and part_out with "
                        "part_slots >= N/64");
         return B2_ERR_ARG;

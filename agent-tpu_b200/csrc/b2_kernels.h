@@ -23,11 +23,15 @@ enum GemmEpilogue {
 // LayerNorm needs (LNRES_STATS). Row statistics travel as float2 (mean, rstd) per row.
 struct GemmLnArgs {
   const float2* row_stats = nullptr;  // LNIN: stats of A's rows. LNRES: stats of the residual rows U
+  // ... or, instead of finished statistics, the partial sums an LNRES_STATS epilogue left behind
+  // ([rows, part_slots] (Σ, Σ²)); every reader adds them in slot order, so all readers agree
+  const float2* part_in = nullptr;
+  float inv_h = 0.f, eps = 0.f;       // 1 / row length and LayerNorm epsilon (with part_in)
   const float* g = nullptr;           // LNIN: column sums of the folded weight (bias slot carries c)
   const float* res_gamma = nullptr;   // LNRES: γ, β of the LayerNorm that produces the residual
   const float* res_beta = nullptr;
   float2* part_out = nullptr;         // LNRES: [rows, part_slots] partial (Σ, Σ²), slot = column/64
-  int part_slots = 0;
+  int part_slots = 0;                 // slots per row of part_in and part_out
 };
 // Tensor maps: A is [M,K] bf16 with row pitch lda elements, W is [N,K] bf16 dense.
 int gemm_tmap_a(CUtensorMap* out, const void* A, int M, int K, int64_t lda);
