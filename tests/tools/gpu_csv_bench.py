@@ -3,7 +3,7 @@
 (b2_csv_open), counted / sliced through `read_csv_shard`, and classified through the chained
 `map_classify_tpu` payload (source_uri). Prints one JSON line per measurement.
 
-    python agent-tpu_b200/tools/gpu_csv_bench.py [rows=2000000] [classify_rows=262144]
+    python tests/tools/gpu_csv_bench.py [rows=2000000] [classify_rows=262144]
 
 The CPU number beside the index is the reference's algorithm (csv.DictReader, oracle/csv_oracle.py)
 counting the same file on one host core (it is a single-threaded C loop)."""
