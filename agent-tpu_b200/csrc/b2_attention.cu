@@ -1,28 +1,31 @@
 // b2_attention.cu — masked self-attention for the encoder, head dim 64, on tcgen05 + TMA.
 //
 // Persistent kernels, two CTAs per SM. A CTA walks its work items through a two-stage ring of
-// {Q, K, V} tiles in shared memory and two S/O accumulators in TMEM:
+// {Q, K, V} tiles in shared memory and 256 columns of tensor memory:
 //   S = Q·Kᵀ            tcgen05.mma 128 x n x 64  (Q, K: K-major 128-byte-swizzled TMA tiles)
 //   P = exp2((S-m)·c)    two threads per query row read S from TMEM; keys >= len are masked out
-//   O = P·V              tcgen05.mma 128 x 64 x n  (P: written bf16 into the swizzled smem of the dead
-//                                                  Q|K tiles as the A operand; V: MN-major TMA tile,
-//                                                  no transpose; O accumulates over S's TMEM columns)
+//   O = P·V              tcgen05.mma 128 x 64 x n  (V: MN-major TMA tile, no transpose)
 // with n = the block's valid keys rounded up to 32: the TMA boxes (four tensor maps with 32, 64, 96
 // and 128 rows), the UMMA N of Q·Kᵀ and the K extent of P·V all shrink with the sequence. Rows of
 // the tiles beyond the box hold stale shared memory; no MMA whose result is kept reads them.
 //
-//   MMA thread     : item i+1's Q·Kᵀ is issued right behind item i's P·V, so the softmax warps never
-//                    wait for Q·Kᵀ.
-//   TMA thread     : item i+2's loads go out as soon as P·V(i) has completed (tiles two further ahead
-//                    are prefetched into L2). Two single-thread roles in two warps, because one
-//                    thread doing both spent 0.8 us per item issuing (dev_check timeline), and
-//                    per-item (length, first row) are looked up once into shared memory: a global
-//                    load in such a dependent chain costs ~0.5 us each time.
-//   softmax warps  : eight per CTA, two threads per query row (keys 0-63 / 64-127, then output columns
-//                    0-31 / 32-63); the row maximum and denominator are exchanged through shared
-//                    memory. This part is a chain of TMEM loads, MUFU.EX2 and row-strided stores: it
-//                    needs warps, not width, to hide its latency (measured with the timeline below:
-//                    2.0 us softmax + 1.0 us store per 128-key item with one thread per row).
+// S = 128 kernel (attention_persist_kernel), per item i:
+//   * P(i) never touches shared memory: the softmax threads write it as packed bf16 over the S
+//     columns they have just consumed and P·V takes its A operand from tensor memory. That halves
+//     the shared-memory traffic of P·V (only V is streamed), removes the row-strided P stores and
+//     the proxy fence from the softmax chain, and frees the Q and K tiles the moment Q·Kᵀ(i) is
+//     done, so {Q, K}(i+2) is requested a whole softmax earlier than V(i+2);
+//   * S has one buffer and O two: Q·Kᵀ(i+1) is issued right behind P·V(i) and the softmax threads
+//     normalise and store O(i-1) while the tensor core works on both, instead of idling until P·V(i)
+//     has finished and then again until Q·Kᵀ(i+1) has (dev_check timeline: 1.0 + 0.7 us of the
+//     former 3.6 us per item were those two waits).
+//   MMA thread / TMA thread: two single-thread roles in two warps, because one thread doing both
+//     spent 0.8 us per item issuing (dev_check timeline); per-item (length, first row) are looked up
+//     once into shared memory: a global load in such a dependent chain costs ~0.5 us each time.
+//     Tiles two items further ahead are prefetched into L2.
+//   softmax warps: eight per CTA, two threads per query row (keys 0-63 / 64-127, then output columns
+//     0-31 / 32-63); the row maximum and denominator are exchanged through shared memory. This part
+//     is a chain of TMEM loads and MUFU.EX2: it needs warps, not width, to hide its latency.
 //
 // attention_persist_kernel  S = 128: one item = (sequence, head), one key block.
 // attention_stream_kernel   S = 256..512: one ring step = (sequence, head, query block, key block);
@@ -62,6 +65,8 @@ struct AttMaps {
 };
 
 enum { QKV_FULL = 0, S_FULL = 1, P_FULL = 2, O_FULL = 3, FREE = 4 };
+// the S = 128 kernel loads {Q, K} and V separately and has no FREE barrier
+enum { QK_FULL = QKV_FULL, V_FULL = FREE };
 
 __device__ __forceinline__ void softmax_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
@@ -89,11 +94,10 @@ __device__ __forceinline__ float softmax_max64(uint32_t tS, int kv) {
   return mx;
 }
 
-// exp2((s - m)·c) for one 32-key chunk -> bf16 P in the swizzled tile row; returns the chunk's sum.
+// exp2((s - m)·c) for one 32-key chunk -> 16 registers of packed bf16 P; returns the chunk's sum.
 // Unmasked chunks: packed FFMA2 / FADD2, two MUFU.EX2 and one bf16x2 convert per key pair.
-__device__ __forceinline__ float softmax_exp32(const uint32_t (&v)[32], int kv_chunk, float sl2, float moff,
-                                               uint8_t* tile_row, int c, int r) {
-  uint32_t packed[16];
+__device__ __forceinline__ float softmax_exp32_regs(const uint32_t (&v)[32], int kv_chunk, float sl2, float moff,
+                                                    uint32_t (&packed)[16]) {
   float sum;
   if (kv_chunk >= 32) {
     const uint64_t scale2 = f32x2(sl2, sl2), shift2 = f32x2(-moff, -moff);
@@ -120,6 +124,14 @@ __device__ __forceinline__ float softmax_exp32(const uint32_t (&v)[32], int kv_c
       packed[j >> 1] = pack_bf16x2(p0, p1);
     }
   }
+  return sum;
+}
+
+// ... -> bf16 P in the swizzled shared-memory tile row (the streaming kernel's A operand)
+__device__ __forceinline__ float softmax_exp32(const uint32_t (&v)[32], int kv_chunk, float sl2, float moff,
+                                               uint8_t* tile_row, int c, int r) {
+  uint32_t packed[16];
+  const float sum = softmax_exp32_regs(v, kv_chunk, sl2, moff, packed);
   // chunk c (0/1) of this 64-key tile -> 16-byte slots (4c + j) ^ (r & 7) of the 128-byte row
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -127,6 +139,27 @@ __device__ __forceinline__ float softmax_exp32(const uint32_t (&v)[32], int kv_c
     *reinterpret_cast<uint4*>(tile_row + slot * 16) =
         make_uint4(packed[j * 4], packed[j * 4 + 1], packed[j * 4 + 2], packed[j * 4 + 3]);
   }
+  return sum;
+}
+
+// P for this thread's half row, written over the S columns it has just consumed: chunk c of the half
+// row (S columns [32c, 32c+32) of the half) becomes 16 columns of packed bf16 at [16c, 16c+16) of the
+// half — the layout tcgen05.mma takes for an A operand in tensor memory.
+__device__ __forceinline__ float softmax_exp64_tmem(uint32_t tS_half, int kv, float sl2, float m_new) {
+  const float moff = m_new * sl2;
+  float sum = 0.f;
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    if (c * 32 < kv) {
+      uint32_t v[32];
+      tmem_ld_32x32(tS_half + c * 32, v);
+      tmem_ld_wait();
+      uint32_t packed[16];
+      sum += softmax_exp32_regs(v, kv - c * 32, sl2, moff, packed);
+      tmem_st_32x16(tS_half + c * 16, packed);
+    }
+  }
+  tmem_st_wait();
   return sum;
 }
 
@@ -190,11 +223,11 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
 
   if (threadIdx.x == ATT_SOFTMAX_THREADS) {
     for (int s = 0; s < 2; ++s) {
-      mbar_init(bar(QKV_FULL, s), 1);
+      mbar_init(bar(QK_FULL, s), 1);
+      mbar_init(bar(V_FULL, s), 1);
       mbar_init(bar(S_FULL, s), 1);
       mbar_init(bar(P_FULL, s), ATT_SOFTMAX_THREADS);
       mbar_init(bar(O_FULL, s), 1);
-      mbar_init(bar(FREE, s), ATT_SOFTMAX_THREADS);
     }
     fence_barrier_init();
   }
@@ -207,17 +240,28 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
   if (warp == 9) {
     // ===== TMA thread =====
     if (lane == 0) {
-      auto load_item = [&](int i) {
+      // {Q, K} and V of an item travel separately: the Q and K tiles are dead as soon as Q·Kᵀ has
+      // completed (P lives in tensor memory), the V tile when P·V has
+      auto load_qk = [&](int i) {
         const int idx = blockIdx.x + i * gridDim.x;
         const int h = idx % heads;
         const int2 md = meta[i];
         const int box = (md.x + 31) >> 5;
         const int s = i & 1;
         const uint32_t st = base + s * STAGE_BYTES;
-        mbar_expect_tx(bar(QKV_FULL, s), 3 * box * 32 * 128);
-        tma_load_2d(st, &maps.m[box - 1], bar(QKV_FULL, s), h * HD, md.y);
-        tma_load_2d(st + TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), hidden + h * HD, md.y);
-        tma_load_2d(st + 2 * TILE_BYTES, &maps.m[box - 1], bar(QKV_FULL, s), 2 * hidden + h * HD, md.y);
+        mbar_expect_tx(bar(QK_FULL, s), 2 * box * 32 * 128);
+        tma_load_2d(st, &maps.m[box - 1], bar(QK_FULL, s), h * HD, md.y);
+        tma_load_2d(st + TILE_BYTES, &maps.m[box - 1], bar(QK_FULL, s), hidden + h * HD, md.y);
+      };
+      auto load_v = [&](int i) {
+        const int idx = blockIdx.x + i * gridDim.x;
+        const int h = idx % heads;
+        const int2 md = meta[i];
+        const int box = (md.x + 31) >> 5;
+        const int s = i & 1;
+        mbar_expect_tx(bar(V_FULL, s), box * 32 * 128);
+        tma_load_2d(base + s * STAGE_BYTES + 2 * TILE_BYTES, &maps.m[box - 1], bar(V_FULL, s),
+                    2 * hidden + h * HD, md.y);
       };
       // pull item i's tiles from DRAM into L2 ahead of its TMA load (no shared memory needed)
       auto prefetch_item = [&](int i) {
@@ -229,16 +273,14 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
         tma_prefetch_2d(&maps.m[box - 1], hidden + h * HD, md.y);
         tma_prefetch_2d(&maps.m[box - 1], 2 * hidden + h * HD, md.y);
       };
-      if (my_items > 0) load_item(0);
-      if (my_items > 1) load_item(1);
+      for (int i = 0; i < 2 && i < my_items; ++i) { load_qk(i); load_v(i); }
       if (my_items > 2) prefetch_item(2);
       if (my_items > 3) prefetch_item(3);
       for (int i = 0; i + 2 < my_items; ++i) {
-        // stage s's shared memory is free as soon as P·V(i) has completed; its TMEM columns are only
-        // needed again by S(i+2), which the MMA thread issues after P_FULL(i+1), i.e. after the
-        // softmax threads have read O(i)
-        mbar_wait(bar(O_FULL, i & 1), (i >> 1) & 1);
-        load_item(i + 2);
+        mbar_wait(bar(S_FULL, 0), i & 1);  // Q·Kᵀ(i) done: its Q and K tiles can be overwritten
+        load_qk(i + 2);
+        mbar_wait(bar(O_FULL, i & 1), (i >> 1) & 1);  // P·V(i) done: so can its V tile
+        load_v(i + 2);
         if (i + 4 < my_items) prefetch_item(i + 4);
         stamp(i, 3);
       }
@@ -247,6 +289,11 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
     // ===== MMA thread =====
     if (lane == 0) {
       constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
+      // TMEM: S(i) in columns [0, 128); the softmax threads overwrite it in place with P(i) (packed
+      // bf16: keys 0-63 in columns [0, 32), keys 64-127 in columns [64, 96)), which P·V(i) then takes
+      // as its A operand straight from tensor memory. O(i) goes to columns [128 + 64·(i&1), +64) and
+      // is read out one item later. The tensor core executes MMAs in issue order, so Q·Kᵀ(i+1),
+      // issued right behind P·V(i), overwrites P(i) only after P·V(i) has consumed it.
       auto issue_s = [&](int i) {
         const int s = i & 1;
         const uint32_t st = base + s * STAGE_BYTES;
@@ -254,34 +301,33 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
         const uint32_t idesc_s = umma_idesc_bf16(128, nk, 0, 0);
         const uint64_t qd = umma_desc_sw128(st, 16, 1024);
         const uint64_t kd = umma_desc_sw128(st + TILE_BYTES, 16, 1024);
-        mbar_wait(bar(QKV_FULL, s), (i >> 1) & 1);
+        mbar_wait(bar(QK_FULL, s), (i >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k)
-          umma_bf16(tmem_base + s * 128, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
-        umma_commit(bar(S_FULL, s));
+        for (int k = 0; k < HD / 16; ++k) umma_bf16(tmem_base, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
+        umma_commit(bar(S_FULL, 0));
       };
       if (my_items > 0) issue_s(0);
       for (int i = 0; i < my_items; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;
-        const uint32_t st = base + s * STAGE_BYTES;
         const int nk16 = (meta[i].x + 31) >> 5 << 1;  // K=16 steps of P·V: keys rounded up to 32, / 16
-        // A = P: K-major, 64 keys per 16 KiB tile, 32 bytes per K=16 step inside the swizzle atom
-        const uint64_t pd0 = umma_desc_sw128(st, 16, 1024);
         // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes (>>4 = 128) per step
-        const uint64_t vd0 = umma_desc_sw128(st + 2 * TILE_BYTES, 8192, 1024);
+        const uint64_t vd0 = umma_desc_sw128(base + s * STAGE_BYTES + 2 * TILE_BYTES, 8192, 1024);
+        mbar_wait(bar(V_FULL, s), ph);
+        // every softmax thread arrives here after it has written its part of P(i) and, before that,
+        // after its read of O(i-2): O buffer i&1 is free
         mbar_wait(bar(P_FULL, s), ph);
         stamp(i, 0);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           if (k < nk16)
-            umma_bf16(tmem_base + s * 128, pd0 + ((k >> 2) * (TILE_BYTES >> 4) + (k & 3) * 2), vd0 + k * 128u,
-                      idesc_o, k != 0);
+            umma_bf16_ts(tmem_base + 128 + s * 64, tmem_base + (k >> 2) * 64 + (k & 3) * 8, vd0 + k * 128u,
+                         idesc_o, k != 0);
         }
         umma_commit(bar(O_FULL, s));
-        if (i + 1 < my_items) issue_s(i + 1);  // right behind P·V: the softmax warps find S ready
+        if (i + 1 < my_items) issue_s(i + 1);
         stamp(i, 1);
       }
     }
@@ -292,58 +338,62 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
     const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
     float* red_max = red;
     float* red_sum = red + 256;
+    const uint32_t tS = tmem_base + lane_base;
+    // O(i) is normalised and stored one item late, in the shadow of Q·Kᵀ(i+2): what it needs is kept
+    // in registers across the iteration
+    float inv_prev = 0.f;
+    bool write_prev = false;
+    __nv_bfloat16* dst_prev = out;
+    auto store_o = [&](int i, float inv, bool write_row, __nv_bfloat16* dst) {
+      mbar_wait(bar(O_FULL, i & 1), (i >> 1) & 1);
+      if (threadIdx.x == 0) stamp(i, 6);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld_32x32(tS + 128 + (i & 1) * 64 + half * 32, v);
+      tmem_ld_wait();
+      if (write_row) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 w;
+          w.x = pack_bf16x2(__uint_as_float(v[j * 8 + 0]) * inv, __uint_as_float(v[j * 8 + 1]) * inv);
+          w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
+          w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
+          w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
+          *reinterpret_cast<uint4*>(dst + j * 8) = w;
+        }
+      }
+      if (threadIdx.x == 0) stamp(i, 7);
+    };
     for (int i = 0; i < my_items; ++i) {
       const int s = i & 1;
-      const uint32_t ph = (i >> 1) & 1;
       const int idx = blockIdx.x + i * gridDim.x;
       const int h = idx % heads;
       const int2 md = meta[i];
       const int len = md.x, row0 = md.y;
       const int kv = min(64, max(0, len - 64 * half));  // valid keys in this thread's half row
-      const uint32_t tS = tmem_base + s * 128 + lane_base;
-      uint8_t* tile_row = smem_aligned + s * STAGE_BYTES + half * TILE_BYTES + r * 128;
-      mbar_wait(bar(S_FULL, s), ph);
+      mbar_wait(bar(S_FULL, 0), i & 1);
       if (threadIdx.x == 0) stamp(i, 4);
       tc_fence_after();
       float mx = kv > 0 ? softmax_max64(tS + 64 * half, kv) : -INFINITY;
       red_max[half * 128 + r] = mx;
       softmax_bar();
       mx = fmaxf(mx, red_max[(half ^ 1) * 128 + r]);
-      float rowsum = kv > 0 ? softmax_exp64(tS + 64 * half, kv, sl2, mx, tile_row, r) : 0.f;
+      float rowsum = kv > 0 ? softmax_exp64_tmem(tS + 64 * half, kv, sl2, mx) : 0.f;
       red_sum[half * 128 + r] = rowsum;
-      fence_proxy_async_smem();  // P was written through the generic proxy; the MMA reads it async
-      tc_fence_before();
+      tc_fence_before();  // orders this thread's TMEM traffic (S(i) read, P(i) written, O(i-2) read)
       mbar_arrive(bar(P_FULL, s));
       if (threadIdx.x == 0) stamp(i, 5);
       softmax_bar();
       rowsum += red_sum[(half ^ 1) * 128 + r];
-      const float inv = rowsum > 0.f ? 1.0f / rowsum : 0.f;
+      // the previous item's output, while the tensor core works on S(i+1) and P·V(i)
+      if (i > 0) store_o(i - 1, inv_prev, write_prev, dst_prev);
+      inv_prev = rowsum > 0.f ? 1.0f / rowsum : 0.f;
       // rows past the sequence's length are pad (padded layout) or belong to the next sequence
       // (packed layout): never written
-      __nv_bfloat16* dst = out + static_cast<size_t>(row0 + r) * hidden + h * HD + half * 32;
-      mbar_wait(bar(O_FULL, s), ph);
-      if (threadIdx.x == 0) stamp(i, 6);
-      tc_fence_after();
-      {
-        uint32_t v[32];
-        tmem_ld_32x32(tS + half * 32, v);
-        tmem_ld_wait();
-        if (r < len) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 w;
-            w.x = pack_bf16x2(__uint_as_float(v[j * 8 + 0]) * inv, __uint_as_float(v[j * 8 + 1]) * inv);
-            w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
-            w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
-            w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + j * 8) = w;
-          }
-        }
-      }
-      tc_fence_before();
-      mbar_arrive(bar(FREE, s));
-      if (threadIdx.x == 0) stamp(i, 7);
+      write_prev = r < len;
+      dst_prev = out + static_cast<size_t>(row0 + r) * hidden + h * HD + half * 32;
     }
+    if (my_items > 0) store_o(my_items - 1, inv_prev, write_prev, dst_prev);
   }
 
   __syncwarp();
