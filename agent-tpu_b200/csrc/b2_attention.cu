@@ -19,6 +19,12 @@
 //     normalise and store O(i-1) while the tensor core works on both, instead of idling until P·V(i)
 //     has finished and then again until Q·Kᵀ(i+1) has (dev_check timeline: 1.0 + 0.7 us of the
 //     former 3.6 us per item were those two waits).
+//     Variants measured and dropped (full-length batch, 0.153 ms as built): P in columns of its own
+//     with Q·Kᵀ(i+1) issued ahead of P·V(i) and a single O buffer — 0.158 ms, because P·V(i) then
+//     waits for the O(i-1) read-out and the next P write waits for P·V(i); one CTA per SM — 0.207 ms.
+//     With 256 of the SM's 512 TMEM columns per CTA there is room for two item buffers, and a
+//     bubble-free schedule needs three; the short MMAs (32-64 cycles of math each) also run at about
+//     half their floor rate when issued in bursts of 12 per item.
 //   MMA thread / TMA thread: two single-thread roles in two warps, because one thread doing both
 //     spent 0.8 us per item issuing (dev_check timeline); per-item (length, first row) are looked up
 //     once into shared memory: a global load in such a dependent chain costs ~0.5 us each time.
@@ -327,6 +333,7 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
                          idesc_o, k != 0);
         }
         umma_commit(bar(O_FULL, s));
+        stamp(i, 2);
         if (i + 1 < my_items) issue_s(i + 1);
         stamp(i, 1);
       }
@@ -669,7 +676,11 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
   int sms = 0;
   B2_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const AttMaps& maps = reinterpret_cast<const AttMaps&>(tqkv);
-  int ctas = items < 2 * sms ? static_cast<int>(items) : 2 * sms;
+  static const int per_sm = [] {  // developer knob: B2_ATT_CTAS_PER_SM=1 runs one CTA per SM
+    const char* e = getenv("B2_ATT_CTAS_PER_SM");
+    return e && atoi(e) == 1 ? 1 : 2;
+  }();
+  int ctas = items < per_sm * sms ? static_cast<int>(items) : per_sm * sms;
   if (S == QB) {
     const int need = static_cast<int>((items + PERSIST_MAX_ITEMS - 1) / PERSIST_MAX_ITEMS);
     if (ctas < need) ctas = need;  // a CTA's item list must fit its shared-memory table
