@@ -383,7 +383,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         "launches": g_n, "share_of_step": round(g_ms / (sum(v["ms"] for v in kern.values()) or 1.0), 4),
         # dram__bytes_read + write per launch, mean of the four encoder GEMMs in one ncu --set full
         # capture at T ~ 71K rows per batch (profiles/r01_ncu_gemm2.md); algorithmic bytes are ~equal
-        "traffic": 464.5e6, "traffic_source": "profiles/r01_ncu_gemm2.md (ncu capture r01b, mean of 4 launches)",
+        "traffic": 467.8e6, "traffic_source": "profiles/r01_ncu_round_end.md (ncu capture r01d, mean of one layer's 4 GEMM launches)",
     }
     whole = {"achieved_tflops": round(value / world * FLOP_PER_ITEM / 1e12, 1),
              "frac_of_sustained": round(value / world * FLOP_PER_ITEM / 1e12 / peaks["bf16_sustained"], 4),
