@@ -191,7 +191,7 @@ def run_reference(args, rank: int, world: int):
         "gpu_launches": 0,
         "note": "reference's own CPU path is a stub that classifies nothing (SURVEY.md G6); this is the oracle port",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -206,9 +206,6 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # keep stdout to the one JSON line: NCCL prints its version banner there at VERSION level
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -287,8 +284,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
 
     if args.profile_run:
         if rank == 0:
-            print(json.dumps({"profile_run": True, "ms_per_step": ms_per_step, "items_per_s": value,
-                              "kernels": kern}), flush=True)
+            emit({"profile_run": True, "ms_per_step": ms_per_step, "items_per_s": value, "kernels": kern})
         eng.close()
         return
 
@@ -419,10 +415,32 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         "roofline": roofline, "kernels": kernels, "whole_path": whole,
         "cpu_baseline": cpu, "clocks": clocks,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def claim_stdout() -> None:
+    """Keep stdout to the one JSON line: from here on file descriptor 1 points at stderr, so whatever
+    a library prints there (NCCL's version banner at NCCL_DEBUG=VERSION or above, for one) cannot land
+    in front of it; `emit` writes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    fd = _REAL_STDOUT if _REAL_STDOUT is not None else 1
+    while data:
+        data = data[os.write(fd, data):]
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
