@@ -126,6 +126,16 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
   constexpr bool kLnRes = EPI == GEMM_EPI_LNRES_STATS;
   constexpr bool kResidual = EPI == GEMM_EPI_BIAS_RESIDUAL || kLnRes;
   if (m_dev) M = min(M, __ldg(m_dev));
+  // developer timeline: pair 0's leader records %globaltimer per tile — [0] accumulator stage free,
+  // [1] main loop issued (MMA thread); [2] staging block free, [3] accumulator ready, [4] residual
+  // landed, [5] first half drained, [6] second half drained, [7] TMA store issued (epilogue warp 0)
+  auto stamp = [&](int tile_it, int slot) {
+    if (ln.trace && blockIdx.x == 0 && tile_it < 32) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      ln.trace[tile_it * 8 + slot] = t;
+    }
+  };
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   const uint32_t sA = base;
@@ -208,6 +218,7 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(tempty_bar(as), aphase ^ 1u);
+        stamp(it, 0);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -222,6 +233,7 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
         umma_commit_2sm(tfull_bar(as), 0b11);  // both accumulator halves complete
+        stamp(it, 1);
       }
     }
   } else if (warp < EPI_WARPS) {
@@ -246,6 +258,7 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // the previous tile's TMA store must have finished reading this staging block
       if (elected) tma_store_wait_read<0>();
       asm volatile("bar.sync %0, 128;" ::"r"(1 + quarter) : "memory");
+      if (warp == 0 && lane == 0) stamp(it, 2);
       if (kResidual && active && elected) {
         mbar_expect_tx(rfull_bar(quarter), OUT_BYTES);
         tma_load_2d(buf, &tmap_r, rfull_bar(quarter), colq, row_base);
@@ -278,8 +291,10 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       float psum = 0.f, psq = 0.f;
       mbar_wait(tfull_bar(as), aphase);
+      if (warp == 0 && lane == 0) stamp(it, 3);
       tc_fence_after();
       if (kResidual && active) mbar_wait(rfull_bar(quarter), it & 1);
+      if (warp == 0 && lane == 0) stamp(it, 4);
       const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + quarter * 64;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -291,6 +306,7 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);  // the issuer waits on the leader's copy
+          if (warp == 0 && lane == 0) stamp(it, 5);
         }
         if (active) {
 #pragma unroll
@@ -365,12 +381,14 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       if (kLnRes && row_ok && active)
         ln.part_out[static_cast<size_t>(row) * ln.part_slots + (colq >> 6)] = make_float2(psum, psq);
+      if (warp == 0 && lane == 0) stamp(it, 6);
       fence_proxy_async_smem();  // staging block written through the generic proxy, read by TMA
       asm volatile("bar.sync %0, 128;" ::"r"(1 + quarter) : "memory");
       if (active && elected) {
         tma_store_2d(&tmap_c, buf, colq, row_base);  // rows >= rows-of-C and columns >= N are clipped
         tma_store_commit();
       }
+      if (warp == 0 && lane == 0) stamp(it, 7);
     }
     if (elected) tma_store_wait_all<0>();  // the staging block must outlive its last store
   }
@@ -383,6 +401,8 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
     tmem_dealloc_2sm(tmem_base, 512);
   }
 }
+
+unsigned long long* g_gemm2_trace = nullptr;
 
 template <int EPI>
 int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
@@ -399,13 +419,17 @@ int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, c
   const int tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN);
   int pairs = num_sms / 2;
   if (tiles < pairs) pairs = tiles;
+  GemmLnArgs args = ln;
+  args.trace = g_gemm2_trace;
   gemm2_bf16_tn_kernel<EPI><<<2 * pairs, THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, tr, bias, M, N, K,
-                                                                       m_dev, ln);
+                                                                       m_dev, args);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }
 
 }  // namespace
+
+void gemm2_set_trace(unsigned long long* dev_buf) { g_gemm2_trace = dev_buf; }
 
 // W tensor map for the pair kernel: each CTA loads 128 rows of W per K step.
 int gemm2_tmap_b(CUtensorMap* out, const void* W, int N, int K) {

@@ -340,6 +340,28 @@ int main(int argc, char** argv) {
     fails += check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, true);
     fails += check_attention(256, 512, 768, {512, 300}, true);
   }
+  if (!strcmp(what, "gemm2trace")) {
+    unsigned long long* dtr; CK(cudaMalloc(&dtr, 32 * 8 * 8));
+    const int shapes[4][3] = {{2304, 768, GEMM_EPI_BIAS}, {768, 768, GEMM_EPI_BIAS_RESIDUAL},
+                              {3072, 768, GEMM_EPI_BIAS_GELU}, {768, 3072, GEMM_EPI_BIAS_RESIDUAL}};
+    for (auto& sh : shapes) {
+      check_gemm(71000, sh[0], sh[1], sh[2], sms, false, true);  // warm
+      CK(cudaMemset(dtr, 0, 32 * 8 * 8));
+      gemm2_set_trace(dtr);
+      check_gemm(71000, sh[0], sh[1], sh[2], sms, false, true);
+      gemm2_set_trace(nullptr);
+      std::vector<unsigned long long> tr(32 * 8);
+      CK(cudaMemcpy(tr.data(), dtr, tr.size() * 8, cudaMemcpyDeviceToHost));
+      const unsigned long long t0 = tr[0];
+      printf("N=%d K=%d epi=%d  tile: mma[stage free, issued] epi[staging free, acc ready, residual, half 1, "
+             "half 2, stored]  (ns)\n", sh[0], sh[1], sh[2]);
+      for (int i = 0; i < 12; ++i) {
+        printf("%2d:", i);
+        for (int k = 0; k < 8; ++k) printf(" %7lld", tr[i * 8 + k] ? (long long)(tr[i * 8 + k] - t0) : -1ll);
+        printf("\n");
+      }
+    }
+  }
   if (!strcmp(what, "atttrace")) {
     unsigned long long* dtr; CK(cudaMalloc(&dtr, 64 * 8 * 8)); CK(cudaMemset(dtr, 0, 64 * 8 * 8));
     check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, false);   // warm
