@@ -134,6 +134,7 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
       unsigned long long t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
       ln.trace[tile_it * 8 + slot] = t;
+      ln.trace[256 + tile_it * 8 + slot] = static_cast<unsigned long long>(clock64());  // SM cycles
     }
   };
   const uint32_t raw = smem_u32(smem_raw);
@@ -199,6 +200,12 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const int brow = n_blk * BN + rank * BNH;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (ln.debug_mode == 1 && (t != pair || kb >= STAGES)) {  // dev_check: MMA-only pace
+            if (leader) mbar_arrive(full_bar(stage));
+            else mbar_arrive_cluster(full_bar(stage), 0);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            continue;
+          }
           if (leader) mbar_expect_tx(full_bar(stage), 2 * STAGE_BYTES);
           else mbar_arrive_cluster(full_bar(stage), 0);
           tma_load_2d_2sm(sA + stage * A_BYTES, &tmap_a, full_bar(stage), kb * BK, arow);
@@ -226,9 +233,11 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tc_fence_after();
           const uint64_t a_desc = umma_desc_sw128(sA + stage * A_BYTES, 16, 1024);
           const uint64_t b_desc = umma_desc_sw128(sB + stage * B_BYTES, 16, 1024);
+          if (ln.debug_mode != 2) {  // 2 (dev_check): TMA-only pace
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16_2sm(d_tmem, a_desc + 2u * k, b_desc + 2u * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16_2sm(d_tmem, a_desc + 2u * k, b_desc + 2u * k, idesc, (kb | k) != 0);
+          }
           umma_commit_2sm(empty_bar(stage), 0b11);  // both CTAs' smem slots are free again
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -403,6 +412,7 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
 }
 
 unsigned long long* g_gemm2_trace = nullptr;
+int g_gemm2_debug = 0;
 
 template <int EPI>
 int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
@@ -421,6 +431,7 @@ int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, c
   if (tiles < pairs) pairs = tiles;
   GemmLnArgs args = ln;
   args.trace = g_gemm2_trace;
+  args.debug_mode = g_gemm2_debug;
   gemm2_bf16_tn_kernel<EPI><<<2 * pairs, THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, tr, bias, M, N, K,
                                                                        m_dev, args);
   B2_CUDA_OK(cudaGetLastError());
@@ -429,7 +440,10 @@ int launch2(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, c
 
 }  // namespace
 
-void gemm2_set_trace(unsigned long long* dev_buf) { g_gemm2_trace = dev_buf; }
+void gemm2_set_trace(unsigned long long* dev_buf, int debug_mode) {
+  g_gemm2_trace = dev_buf;
+  g_gemm2_debug = debug_mode;
+}
 
 // W tensor map for the pair kernel: each CTA loads 128 rows of W per K step.
 int gemm2_tmap_b(CUtensorMap* out, const void* W, int N, int K) {

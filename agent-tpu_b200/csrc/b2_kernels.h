@@ -33,6 +33,7 @@ struct GemmLnArgs {
   float2* part_out = nullptr;         // LNRES: [rows, part_slots] partial (Σ, Σ²), slot = column/64
   int part_slots = 0;                 // slots per row of part_in and part_out
   unsigned long long* trace = nullptr;  // developer timeline (dev_check gemm2trace), else null
+  int debug_mode = 0;  // dev_check only: 1 = no TMA loads after the first ring fill, 2 = no MMAs (results garbage)
 };
 // Tensor maps: A is [M,K] bf16 with row pitch lda elements, W is [N,K] bf16 dense.
 int gemm_tmap_a(CUtensorMap* out, const void* A, int M, int K, int64_t lda);
@@ -67,7 +68,7 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
                    const int32_t* lens, int B, int S, int hidden, const int32_t* cu = nullptr);
 
 void attention_set_trace(unsigned long long* dev_buf);  // developer timeline hook (dev_check)
-void gemm2_set_trace(unsigned long long* dev_buf);      // same for the pair GEMM
+void gemm2_set_trace(unsigned long long* dev_buf, int debug_mode = 0);  // same for the pair GEMM
 
 // ---- element-wise / row kernels (b2_rows.cu) ---------------------------------------------------
 // out[row] = LayerNorm(word[ids[row]] + pos[row % S] + type[0]) * gamma + beta  -> bf16

@@ -341,18 +341,22 @@ int main(int argc, char** argv) {
     fails += check_attention(256, 512, 768, {512, 300}, true);
   }
   if (!strcmp(what, "gemm2trace")) {
-    unsigned long long* dtr; CK(cudaMalloc(&dtr, 32 * 8 * 8));
+    unsigned long long* dtr; CK(cudaMalloc(&dtr, 2 * 32 * 8 * 8));
     const int shapes[4][3] = {{2304, 768, GEMM_EPI_BIAS}, {768, 768, GEMM_EPI_BIAS_RESIDUAL},
                               {3072, 768, GEMM_EPI_BIAS_GELU}, {768, 3072, GEMM_EPI_BIAS_RESIDUAL}};
     for (auto& sh : shapes) {
       check_gemm(71000, sh[0], sh[1], sh[2], sms, false, true);  // warm
-      CK(cudaMemset(dtr, 0, 32 * 8 * 8));
-      gemm2_set_trace(dtr);
+      CK(cudaMemset(dtr, 0, 2 * 32 * 8 * 8));
+      const int dbg = getenv("B2_GEMM2_DEBUG") ? atoi(getenv("B2_GEMM2_DEBUG")) : 0;
+      gemm2_set_trace(dtr, dbg);
       check_gemm(71000, sh[0], sh[1], sh[2], sms, false, true);
-      gemm2_set_trace(nullptr);
-      std::vector<unsigned long long> tr(32 * 8);
+      gemm2_set_trace(nullptr, 0);
+      std::vector<unsigned long long> tr(2 * 32 * 8);
       CK(cudaMemcpy(tr.data(), dtr, tr.size() * 8, cudaMemcpyDeviceToHost));
       const unsigned long long t0 = tr[0];
+      printf("SM clock during the run: %.0f MHz; main loop of tile 5: %lld cycles\n",
+             1e3 * double(tr[256 + 11 * 8] - tr[256]) / double(tr[11 * 8] - tr[0]),
+             (long long)(tr[256 + 5 * 8 + 1] - tr[256 + 5 * 8]));
       printf("N=%d K=%d epi=%d  tile: mma[stage free, issued] epi[staging free, acc ready, residual, half 1, "
              "half 2, stored]  (ns)\n", sh[0], sh[1], sh[2]);
       for (int i = 0; i < 12; ++i) {
