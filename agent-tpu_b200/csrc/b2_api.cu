@@ -105,6 +105,28 @@ enum Kind {
 
 using namespace b2;
 
+// Everything one batch in flight needs (rows = max_batch * max_len).
+struct BatchBuffers {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;  // recorded behind the lane's last batch of a tokenizer run / job
+  int32_t *ids = nullptr, *lens = nullptr;
+  uint8_t* mask = nullptr;
+  __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *ffn = nullptr,
+                *pooled = nullptr;
+  CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{};  // A operands; also TMA store / residual maps
+  CUtensorMap tm_qkv_c{};                          // qkv as a GEMM output
+  AttentionMaps tm_att{};
+  // packed (padding-free) layout: token rows of a batch are stored back to back, sequence b at
+  // rows [cu[b], cu[b+1]); cu[B] is the batch's row count, read by the kernels from device memory
+  int32_t* cu = nullptr;
+  // folded LayerNorm: (mean, rstd) per row and the partial sums they are made from
+  float2 *stats_a = nullptr, *stats_b = nullptr, *part = nullptr, *part_b = nullptr;
+  // [CLS]-only tail of the last layer: after its attention only row 0 of every sequence feeds the
+  // pooler, so the out-projection, FFN and both LayerNorms of that layer run on [B, *] blocks
+  __nv_bfloat16 *cls = nullptr, *cls_ctx = nullptr, *cls_y = nullptr, *cls_f = nullptr;
+  CUtensorMap tm_cls{}, tm_cls_ctx{}, tm_cls_y{}, tm_cls_f{};
+};
+
 struct b2_handle {
   int device = 0;
   int num_sms = 0;
@@ -126,31 +148,21 @@ struct b2_handle {
   std::vector<void*> allocations;
 
   int max_batch = 1024, max_len = 128;
-  // activations for one batch (rows = max_batch * max_len)
-  int32_t *ids = nullptr, *lens = nullptr;
-  uint8_t* mask = nullptr;
-  __nv_bfloat16 *x = nullptr, *qkv = nullptr, *ctx = nullptr, *y = nullptr, *ffn = nullptr,
-                *pooled = nullptr;
-  CUtensorMap tm_x{}, tm_ctx{}, tm_y{}, tm_ffn{};  // A operands; also TMA store / residual maps
-  CUtensorMap tm_qkv_c{};                          // qkv as a GEMM output
-  AttentionMaps tm_att{};
+  // Two sets of per-batch buffers, each with its own stream: consecutive batches of a job alternate
+  // between them, so the ragged end of one batch's kernels (a last wave that fills 27% of the SMs,
+  // the few microseconds every launch needs to ramp up and drain, the small bandwidth-bound kernels
+  // between the GEMMs) is covered by the other batch's work. lane[0] runs on `stream`.
+  BatchBuffers lane[2];
+  int n_lanes = 1;
   unsigned long long* hist = nullptr;
   int64_t* d_tokens = nullptr;  // running sum of lens
-  // packed (padding-free) layout: token rows of a batch are stored back to back, sequence b at
-  // rows [cu[b], cu[b+1]); cu[B] is the batch's row count, read by the kernels from device memory
-  bool packed = true;
-  bool pair_gemm = true;  // CTA-pair GEMM for the encoder projections (B2_GEMM_1CTA=1 turns it off)
+  bool packed = true;      // padding-free token rows (B2_FORCE_PADDED=1 turns it off)
+  bool pair_gemm = true;   // CTA-pair GEMM for the encoder projections (B2_GEMM_1CTA=1 turns it off)
   // LayerNorm folding (B2_NO_LN_FOLD=1 turns it off): no LayerNorm kernel runs in the encoder; the
-  // un-normalised sums stay in x / y and (mean, rstd) per row travel in stats_a / stats_b
+  // un-normalised sums stay in x / y and the row statistics travel beside them
   bool fold_ln = true;
-  float2 *stats_a = nullptr, *stats_b = nullptr, *part = nullptr, *part_b = nullptr;
   float *ones = nullptr, *zeros = nullptr;
   int part_slots = 0;
-  int32_t* cu = nullptr;
-  // [CLS]-only tail of the last layer: after its attention only row 0 of every sequence feeds the
-  // pooler, so the out-projection, FFN and both LayerNorms of that layer run on [B, *] blocks
-  __nv_bfloat16 *cls = nullptr, *cls_ctx = nullptr, *cls_y = nullptr, *cls_f = nullptr;
-  CUtensorMap tm_cls{}, tm_cls_ctx{}, tm_cls_y{}, tm_cls_f{};
 
   // token ids / lengths of a run of items of the job: the tokenizer runs once per TOKENIZE_RUN items
   // (one launch fills the GPU; one launch per 1,024-item batch leaves most of it idle)
@@ -172,6 +184,7 @@ struct b2_handle {
   std::vector<int> event_kinds;
   size_t n_events = 0;
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  cudaEvent_t ev_run = nullptr;  // inputs of the current tokenizer run / job are ready (lane 1 waits on it)
 };
 
 namespace b2 {
@@ -370,61 +383,81 @@ int load_model(b2_handle* h, const char* path) {
   return B2_OK;
 }
 
-int alloc_activations(b2_handle* h) {
+int alloc_lane(b2_handle* h, BatchBuffers& L) {
   const ModelHeader& m = h->mh;
   const int64_t rows = int64_t(h->max_batch) * h->max_len;
   const int64_t H = m.hidden, I = m.intermediate;
   int rc;
   auto A = [&](void** p, int64_t bytes) { h->activation_bytes += bytes; return dev_alloc(h, p, bytes); };
-  if ((rc = A(reinterpret_cast<void**>(&h->ids), rows * 4))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->mask), rows))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->lens), h->max_batch * 4))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->d_tokens), 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.ids), rows * 4))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.mask), rows))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.lens), h->max_batch * 4))) return rc;
   if (!h->has_model) return B2_OK;
-  if ((rc = A(reinterpret_cast<void**>(&h->x), rows * H * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->qkv), rows * 3 * H * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->ctx), rows * H * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->y), rows * H * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->ffn), rows * I * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->pooled), int64_t(h->max_batch) * H * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->hist), int64_t(m.num_labels) * 8))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->cu), (int64_t(h->max_batch) + 1) * 4))) return rc;
-  h->part_slots = static_cast<int>((H + 63) / 64);
-  if ((rc = A(reinterpret_cast<void**>(&h->stats_a), rows * 8))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->stats_b), rows * 8))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->part), rows * h->part_slots * 8))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->part_b), rows * h->part_slots * 8))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->ones), H * 4))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->zeros), H * 4))) return rc;
-  B2_CUDA_OK(cudaMemsetAsync(h->zeros, 0, H * 4, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->part, 0, rows * h->part_slots * 8, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->part_b, 0, rows * h->part_slots * 8, h->stream));
-  if ((rc = fill_synthetic_f32(h->stream, h->ones, H, 0, 0, 0.0f, 1.0f))) return rc;  // 0*x + 1
-  if ((rc = A(reinterpret_cast<void**>(&h->cls), int64_t(h->max_batch) * H * 2))) return rc;
-  B2_CUDA_OK(cudaMemsetAsync(h->cls, 0, int64_t(h->max_batch) * H * 2, h->stream));
-  if ((rc = gemm_tmap_a(&h->tm_cls, h->cls, h->max_batch, H, H))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->cls_ctx), int64_t(h->max_batch) * H * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->cls_y), int64_t(h->max_batch) * H * 2))) return rc;
-  if ((rc = A(reinterpret_cast<void**>(&h->cls_f), int64_t(h->max_batch) * I * 2))) return rc;
-  B2_CUDA_OK(cudaMemsetAsync(h->cls_ctx, 0, int64_t(h->max_batch) * H * 2, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->cls_y, 0, int64_t(h->max_batch) * H * 2, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->cls_f, 0, int64_t(h->max_batch) * I * 2, h->stream));
-  if ((rc = gemm_tmap_a(&h->tm_cls_ctx, h->cls_ctx, h->max_batch, H, H))) return rc;
-  if ((rc = gemm_tmap_a(&h->tm_cls_y, h->cls_y, h->max_batch, H, H))) return rc;
-  if ((rc = gemm_tmap_a(&h->tm_cls_f, h->cls_f, h->max_batch, I, I))) return rc;
+  B2_CUDA_OK(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+  if ((rc = A(reinterpret_cast<void**>(&L.x), rows * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.qkv), rows * 3 * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.ctx), rows * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.y), rows * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.ffn), rows * I * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.pooled), int64_t(h->max_batch) * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.cu), (int64_t(h->max_batch) + 1) * 4))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.stats_a), rows * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.stats_b), rows * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.part), rows * h->part_slots * 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.part_b), rows * h->part_slots * 8))) return rc;
+  B2_CUDA_OK(cudaMemsetAsync(L.part, 0, rows * h->part_slots * 8, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(L.part_b, 0, rows * h->part_slots * 8, h->stream));
+  if ((rc = A(reinterpret_cast<void**>(&L.cls), int64_t(h->max_batch) * H * 2))) return rc;
+  B2_CUDA_OK(cudaMemsetAsync(L.cls, 0, int64_t(h->max_batch) * H * 2, h->stream));
+  if ((rc = gemm_tmap_a(&L.tm_cls, L.cls, h->max_batch, H, H))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.cls_ctx), int64_t(h->max_batch) * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.cls_y), int64_t(h->max_batch) * H * 2))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&L.cls_f), int64_t(h->max_batch) * I * 2))) return rc;
+  B2_CUDA_OK(cudaMemsetAsync(L.cls_ctx, 0, int64_t(h->max_batch) * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(L.cls_y, 0, int64_t(h->max_batch) * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(L.cls_f, 0, int64_t(h->max_batch) * I * 2, h->stream));
+  if ((rc = gemm_tmap_a(&L.tm_cls_ctx, L.cls_ctx, h->max_batch, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&L.tm_cls_y, L.cls_y, h->max_batch, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&L.tm_cls_f, L.cls_f, h->max_batch, I, I))) return rc;
   // pad rows are read by TMA boxes and attention tiles before they are ever written: give them
   // finite contents once so no NaN bit pattern can reach a masked-out product
-  B2_CUDA_OK(cudaMemsetAsync(h->x, 0, rows * H * 2, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->qkv, 0, rows * 3 * H * 2, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->ctx, 0, rows * H * 2, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->y, 0, rows * H * 2, h->stream));
-  B2_CUDA_OK(cudaMemsetAsync(h->ffn, 0, rows * I * 2, h->stream));
-  if ((rc = gemm_tmap_a(&h->tm_x, h->x, rows, H, H))) return rc;
-  if ((rc = gemm_tmap_a(&h->tm_ctx, h->ctx, rows, H, H))) return rc;
-  if ((rc = gemm_tmap_a(&h->tm_y, h->y, rows, H, H))) return rc;
-  if ((rc = gemm_tmap_a(&h->tm_ffn, h->ffn, rows, I, I))) return rc;
-  if ((rc = gemm2_tmap_c(&h->tm_qkv_c, h->qkv, rows, 3 * H, 3 * H))) return rc;
-  if ((rc = attention_tmaps(&h->tm_att, h->qkv, rows, H))) return rc;
+  B2_CUDA_OK(cudaMemsetAsync(L.x, 0, rows * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(L.qkv, 0, rows * 3 * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(L.ctx, 0, rows * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(L.y, 0, rows * H * 2, h->stream));
+  B2_CUDA_OK(cudaMemsetAsync(L.ffn, 0, rows * I * 2, h->stream));
+  if ((rc = gemm_tmap_a(&L.tm_x, L.x, rows, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&L.tm_ctx, L.ctx, rows, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&L.tm_y, L.y, rows, H, H))) return rc;
+  if ((rc = gemm_tmap_a(&L.tm_ffn, L.ffn, rows, I, I))) return rc;
+  if ((rc = gemm2_tmap_c(&L.tm_qkv_c, L.qkv, rows, 3 * H, 3 * H))) return rc;
+  if ((rc = attention_tmaps(&L.tm_att, L.qkv, rows, H))) return rc;
+  return B2_OK;
+}
+
+int alloc_activations(b2_handle* h) {
+  const ModelHeader& m = h->mh;
+  const int64_t H = m.hidden;
+  int rc;
+  auto A = [&](void** p, int64_t bytes) { h->activation_bytes += bytes; return dev_alloc(h, p, bytes); };
+  if ((rc = A(reinterpret_cast<void**>(&h->d_tokens), 8))) return rc;
+  h->lane[0].stream = h->stream;
+  h->n_lanes = 1;
+  if (h->has_model) {
+    if ((rc = A(reinterpret_cast<void**>(&h->hist), int64_t(m.num_labels) * 8))) return rc;
+    h->part_slots = static_cast<int>((H + 63) / 64);
+    if ((rc = A(reinterpret_cast<void**>(&h->ones), H * 4))) return rc;
+    if ((rc = A(reinterpret_cast<void**>(&h->zeros), H * 4))) return rc;
+    B2_CUDA_OK(cudaMemsetAsync(h->zeros, 0, H * 4, h->stream));
+    if ((rc = fill_synthetic_f32(h->stream, h->ones, H, 0, 0, 0.0f, 1.0f))) return rc;  // 0*x + 1
+    const char* one = getenv("B2_ONE_LANE");
+    if (!(one && one[0] == '1')) {
+      B2_CUDA_OK(cudaStreamCreateWithFlags(&h->lane[1].stream, cudaStreamNonBlocking));
+      h->n_lanes = 2;
+    }
+  }
+  for (int l = 0; l < h->n_lanes; ++l)
+    if ((rc = alloc_lane(h, h->lane[l]))) return rc;
   B2_CUDA_OK(cudaStreamSynchronize(h->stream));
   return B2_OK;
 }
@@ -441,7 +474,7 @@ __global__ void sum_lens_kernel(const int32_t* lens, int n, int64_t* total) {
   if (threadIdx.x == 0) {
     long long t = 0;
     for (int w = 0; w < (blockDim.x >> 5); ++w) t += part[w];
-    *total += t;
+    atomicAdd(reinterpret_cast<unsigned long long*>(total), static_cast<unsigned long long>(t));  // two lanes
   }
 }
 
@@ -451,22 +484,22 @@ __global__ void hist_to_i64_kernel(const unsigned long long* src, int64_t* dst, 
 }
 
 // Encoder + head for one batch: ids [B, S] and lens [B] in device memory.
-int forward_batch(b2_handle* h, const int32_t* ids, const int32_t* lens, int B, int S, int topk,
+int forward_batch(b2_handle* h, BatchBuffers& bb, const int32_t* ids, const int32_t* lens, int B, int S, int topk,
                   int32_t* d_top_idx, float* d_top_score, int32_t* d_labels, float* d_logits,
                   int64_t* launches) {
   const ModelHeader& m = h->mh;
   const int H = m.hidden, I = m.intermediate, M = B * S;
-  cudaStream_t st = h->stream;
+  cudaStream_t st = bb.stream;
   int rc;
   // packed layout: M is only the upper bound; the kernels read the true row count from cu[B]
-  const int32_t* cu = h->packed ? h->cu : nullptr;
-  const int32_t* m_dev = h->packed ? h->cu + B : nullptr;
+  const int32_t* cu = h->packed ? bb.cu : nullptr;
+  const int32_t* m_dev = h->packed ? bb.cu + B : nullptr;
   mark(h, K_EMBED);
   if (h->packed) {
-    if ((rc = pack_offsets(st, lens, B, h->cu))) return rc;
+    if ((rc = pack_offsets(st, lens, B, bb.cu))) return rc;
     ++*launches;
   }
-  if ((rc = embed_layernorm(st, ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, h->x,
+  if ((rc = embed_layernorm(st, ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, bb.x,
                             M, S, H, m.vocab_size, h->packed ? lens : nullptr, cu))) return rc;
   ++*launches;
   // encoder projections: CTA-pair kernel when the batch is large enough to fill 74 pairs
@@ -483,13 +516,13 @@ int forward_batch(b2_handle* h, const int32_t* ids, const int32_t* lens, int B, 
   // Row statistics reach the consuming epilogues as the 12 partial (Σ, Σ²) slots the producing GEMM
   // wrote (in_part; summed in slot order by every reader) — except for the embedding output, which
   // is already normalised (identity statistics in stats_b).
-  const float2* in_stats = h->stats_b;
+  const float2* in_stats = bb.stats_b;
   const float2* in_part = nullptr;
   const float inv_h = 1.0f / static_cast<float>(H);
   const float* in_g = h->ones;
   const float* in_b = h->zeros;
   if (fold) {
-    if ((rc = ln_stats_identity(st, h->stats_b, M))) return rc;  // the embedding output is normalised
+    if ((rc = ln_stats_identity(st, bb.stats_b, M))) return rc;  // the embedding output is normalised
     ++*launches;
   }
   auto gemm_ln = [&](const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias,
@@ -503,41 +536,41 @@ int forward_batch(b2_handle* h, const int32_t* ids, const int32_t* lens, int B, 
       GemmLnArgs a;
       a.row_stats = in_stats; a.part_in = in_part; a.part_slots = h->part_slots; a.inv_h = inv_h; a.eps = m.ln_eps;
       a.g = L.g_qkv;
-      if ((rc = gemm_ln(h->tm_x, L.tm2_qkv_f, h->tm_qkv_c, L.c_qkv, nullptr, 3 * H, H, GEMM_EPI_LNIN, a)))
+      if ((rc = gemm_ln(bb.tm_x, L.tm2_qkv_f, bb.tm_qkv_c, L.c_qkv, nullptr, 3 * H, H, GEMM_EPI_LNIN, a)))
         return rc;
-    } else if ((rc = gemm(h->tm_x, L.tm_qkv, L.tm2_qkv, h->tm_qkv_c, h->qkv, L.bqkv, nullptr, nullptr, 3 * H, H,
+    } else if ((rc = gemm(bb.tm_x, L.tm_qkv, L.tm2_qkv, bb.tm_qkv_c, bb.qkv, L.bqkv, nullptr, nullptr, 3 * H, H,
                           3 * H, 0, GEMM_EPI_BIAS))) {
       return rc;
     }
     mark(h, K_ATTENTION);
-    if ((rc = attention_bf16(st, h->tm_att, h->ctx, lens, B, S, H, cu))) return rc;
+    if ((rc = attention_bf16(st, bb.tm_att, bb.ctx, lens, B, S, H, cu))) return rc;
     if (l + 1 == m.layers) {
       // last layer: only the [CLS] rows are read downstream (pooler), and every remaining kernel is
       // row-wise, so run them on the B gathered rows; per-row results are unchanged
       mark(h, K_GEMM_OUT);
-      if ((rc = gather_cls_rows(st, h->ctx, cu, S, B, H, h->cls_ctx))) return rc;
+      if ((rc = gather_cls_rows(st, bb.ctx, cu, S, B, H, bb.cls_ctx))) return rc;
       if (fold) {
         if (in_part) {  // the gather wants finished (mean, rstd): one finalize per batch, not one per GEMM
-          if ((rc = ln_stats_finalize(st, in_part, h->part_slots, M, H, m.ln_eps, h->stats_a, m_dev))) return rc;
-          in_stats = h->stats_a;
+          if ((rc = ln_stats_finalize(st, in_part, h->part_slots, M, H, m.ln_eps, bb.stats_a, m_dev))) return rc;
+          in_stats = bb.stats_a;
           ++*launches;
         }
-        if ((rc = gather_cls_rows_norm(st, h->x, in_stats, in_g, in_b, cu, S, B, H, h->cls))) return rc;
-      } else if ((rc = gather_cls_rows(st, h->x, cu, S, B, H, h->cls))) {
+        if ((rc = gather_cls_rows_norm(st, bb.x, in_stats, in_g, in_b, cu, S, B, H, bb.cls))) return rc;
+      } else if ((rc = gather_cls_rows(st, bb.x, cu, S, B, H, bb.cls))) {
         return rc;
       }
-      if ((rc = gemm_bf16_tn(st, h->tm_cls_ctx, L.tm_o, h->cls_y, L.bo, h->cls, B, H, H, H, H,
+      if ((rc = gemm_bf16_tn(st, bb.tm_cls_ctx, L.tm_o, bb.cls_y, L.bo, bb.cls, B, H, H, H, H,
                              GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
       mark(h, K_LAYERNORM);
-      if ((rc = layernorm_inplace(st, h->cls_y, L.ln1_g, L.ln1_b, m.ln_eps, B, H))) return rc;
+      if ((rc = layernorm_inplace(st, bb.cls_y, L.ln1_g, L.ln1_b, m.ln_eps, B, H))) return rc;
       mark(h, K_GEMM_FFN1);
-      if ((rc = gemm_bf16_tn(st, h->tm_cls_y, L.tm_1, h->cls_f, L.b1, nullptr, B, I, H, I, 0,
+      if ((rc = gemm_bf16_tn(st, bb.tm_cls_y, L.tm_1, bb.cls_f, L.b1, nullptr, B, I, H, I, 0,
                              GEMM_EPI_BIAS_GELU, h->num_sms))) return rc;
       mark(h, K_GEMM_FFN2);
-      if ((rc = gemm_bf16_tn(st, h->tm_cls_f, L.tm_2, h->cls, L.b2, h->cls_y, B, H, I, H, H,
+      if ((rc = gemm_bf16_tn(st, bb.tm_cls_f, L.tm_2, bb.cls, L.b2, bb.cls_y, B, H, I, H, H,
                              GEMM_EPI_BIAS_RESIDUAL, h->num_sms))) return rc;
       mark(h, K_LAYERNORM);
-      if ((rc = layernorm_inplace(st, h->cls, L.ln2_g, L.ln2_b, m.ln_eps, B, H))) return rc;
+      if ((rc = layernorm_inplace(st, bb.cls, L.ln2_g, L.ln2_b, m.ln_eps, B, H))) return rc;
       *launches += 9;
       break;
     }
@@ -546,52 +579,52 @@ int forward_batch(b2_handle* h, const int32_t* ids, const int32_t* lens, int B, 
       mark(h, K_GEMM_OUT);
       a.row_stats = in_stats; a.part_in = in_part; a.inv_h = inv_h; a.eps = m.ln_eps;
       a.res_gamma = in_g; a.res_beta = in_b;
-      a.part_out = h->part; a.part_slots = h->part_slots;  // statistics of y
-      if ((rc = gemm_ln(h->tm_ctx, L.tm2_o, h->tm_y, L.bo, &h->tm_x, H, H, GEMM_EPI_LNRES_STATS, a))) return rc;
+      a.part_out = bb.part; a.part_slots = h->part_slots;  // statistics of y
+      if ((rc = gemm_ln(bb.tm_ctx, L.tm2_o, bb.tm_y, L.bo, &bb.tm_x, H, H, GEMM_EPI_LNRES_STATS, a))) return rc;
       // y's statistics feed the two widest epilogues (FFN1 has 12 column tiles per row block, each
       // of which would re-add the 12 slots): finish them once; x's statistics (below) are read as
       // partials by QKV and the out-projection, which saves the second finalize of the layer
       mark(h, K_LAYERNORM);
-      if ((rc = ln_stats_finalize(st, h->part, h->part_slots, M, H, m.ln_eps, h->stats_a, m_dev))) return rc;
+      if ((rc = ln_stats_finalize(st, bb.part, h->part_slots, M, H, m.ln_eps, bb.stats_a, m_dev))) return rc;
       mark(h, K_GEMM_FFN1);
       GemmLnArgs f1;
-      f1.row_stats = h->stats_a;
+      f1.row_stats = bb.stats_a;
       f1.g = L.g_1;
-      if ((rc = gemm_ln(h->tm_y, L.tm2_1_f, h->tm_ffn, L.c_1, nullptr, I, H, GEMM_EPI_LNIN_GELU, f1)))
+      if ((rc = gemm_ln(bb.tm_y, L.tm2_1_f, bb.tm_ffn, L.c_1, nullptr, I, H, GEMM_EPI_LNIN_GELU, f1)))
         return rc;
       mark(h, K_GEMM_FFN2);
       GemmLnArgs f2;
-      f2.row_stats = h->stats_a;
+      f2.row_stats = bb.stats_a;
       f2.res_gamma = L.ln1_g; f2.res_beta = L.ln1_b;
-      f2.part_out = h->part_b; f2.part_slots = h->part_slots;  // statistics of the next layer's x
-      if ((rc = gemm_ln(h->tm_ffn, L.tm2_2, h->tm_x, L.b2, &h->tm_y, H, I, GEMM_EPI_LNRES_STATS, f2))) return rc;
-      in_part = h->part_b; in_g = L.ln2_g; in_b = L.ln2_b;
+      f2.part_out = bb.part_b; f2.part_slots = h->part_slots;  // statistics of the next layer's x
+      if ((rc = gemm_ln(bb.tm_ffn, L.tm2_2, bb.tm_x, L.b2, &bb.tm_y, H, I, GEMM_EPI_LNRES_STATS, f2))) return rc;
+      in_part = bb.part_b; in_g = L.ln2_g; in_b = L.ln2_b;
       *launches += 6;
       continue;
     }
     mark(h, K_GEMM_OUT);
-    if ((rc = gemm(h->tm_ctx, L.tm_o, L.tm2_o, h->tm_y, h->y, L.bo, &h->tm_x, h->x, H, H, H, H,
+    if ((rc = gemm(bb.tm_ctx, L.tm_o, L.tm2_o, bb.tm_y, bb.y, L.bo, &bb.tm_x, bb.x, H, H, H, H,
                    GEMM_EPI_BIAS_RESIDUAL)))
       return rc;
     mark(h, K_LAYERNORM);
-    if ((rc = layernorm_inplace(st, h->y, L.ln1_g, L.ln1_b, m.ln_eps, M, H, m_dev))) return rc;
+    if ((rc = layernorm_inplace(st, bb.y, L.ln1_g, L.ln1_b, m.ln_eps, M, H, m_dev))) return rc;
     mark(h, K_GEMM_FFN1);
-    if ((rc = gemm(h->tm_y, L.tm_1, L.tm2_1, h->tm_ffn, h->ffn, L.b1, nullptr, nullptr, I, H, I, 0,
+    if ((rc = gemm(bb.tm_y, L.tm_1, L.tm2_1, bb.tm_ffn, bb.ffn, L.b1, nullptr, nullptr, I, H, I, 0,
                    GEMM_EPI_BIAS_GELU)))
       return rc;
     mark(h, K_GEMM_FFN2);
-    if ((rc = gemm(h->tm_ffn, L.tm_2, L.tm2_2, h->tm_x, h->x, L.b2, &h->tm_y, h->y, H, I, H, H,
+    if ((rc = gemm(bb.tm_ffn, L.tm_2, L.tm2_2, bb.tm_x, bb.x, L.b2, &bb.tm_y, bb.y, H, I, H, H,
                    GEMM_EPI_BIAS_RESIDUAL)))
       return rc;
     mark(h, K_LAYERNORM);
-    if ((rc = layernorm_inplace(st, h->x, L.ln2_g, L.ln2_b, m.ln_eps, M, H, m_dev))) return rc;
+    if ((rc = layernorm_inplace(st, bb.x, L.ln2_g, L.ln2_b, m.ln_eps, M, H, m_dev))) return rc;
     *launches += 7;
   }
   mark(h, K_POOLER);
-  if ((rc = gemm_bf16_tn(st, h->tm_cls, h->tm_p, h->pooled, h->bp, nullptr, B, H, H, H, 0,
+  if ((rc = gemm_bf16_tn(st, bb.tm_cls, h->tm_p, bb.pooled, h->bp, nullptr, B, H, H, H, 0,
                          GEMM_EPI_BIAS_TANH, h->num_sms))) return rc;
   mark(h, K_HEAD);
-  if ((rc = classify_head(st, h->pooled, H, h->Wc, h->bc, B, H, m.num_labels, topk, d_logits,
+  if ((rc = classify_head(st, bb.pooled, H, h->Wc, h->bc, B, H, m.num_labels, topk, d_logits,
                           d_top_idx, d_top_score, d_labels, h->hist))) return rc;
   *launches += 2;
   return B2_OK;
@@ -683,35 +716,60 @@ int classify_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offset
     if ((rc = grow(reinterpret_cast<void**>(&h->job_lens), &h->job_lens_cap, size_t(cap) * 4))) return rc;
   }
   int64_t run0 = 0;  // first item of the current tokenizer run
+  // Batches alternate between the lanes (one lane while profiling: its events live on one stream).
+  const int lanes = h->profiling ? 1 : h->n_lanes;
+  bool lane1_busy = false;  // lane 1 has work the main stream has not waited for yet
+  auto join_lane1 = [&]() -> int {
+    if (!lane1_busy) return B2_OK;
+    B2_CUDA_OK(cudaEventRecord(h->lane[1].done, h->lane[1].stream));
+    B2_CUDA_OK(cudaStreamWaitEvent(st, h->lane[1].done, 0));
+    lane1_busy = false;
+    return B2_OK;
+  };
+  if (!d_utf8 && lanes > 1) B2_CUDA_OK(cudaEventRecord(h->ev_run, st));  // staged ids, cleared counters
+  bool lane1_synced = false;  // lane 1 has waited on ev_run since it was last recorded
   // labels are needed for the histogram even when the caller does not want them
   for (int64_t i0 = 0; i0 < n; i0 += h->max_batch) {
     const int B = static_cast<int>(std::min<int64_t>(h->max_batch, n - i0));
-    const int32_t *ids = h->ids, *lens = h->lens;
+    const int li = lanes > 1 ? static_cast<int>(batches & 1) : 0;
+    BatchBuffers& bb = h->lane[li];
+    const int32_t *ids = bb.ids, *lens = bb.lens;
     if (d_utf8) {
       if (i0 == 0 || i0 >= run0 + run_items) {
         run0 = i0;
         const int run_n = static_cast<int>(std::min<int64_t>(run_items, n - run0));
+        if ((rc = join_lane1())) return rc;  // lane 1 may still be reading the previous run's ids
         mark(h, K_TOKENIZE);
         if ((rc = tokenizer_run(st, h->tok, d_utf8, d_offsets + run0, run_n, max_len, h->job_ids, nullptr,
                                 h->job_lens, h->num_sms))) return rc;
         sum_lens_kernel<<<1, 1024, 0, st>>>(h->job_lens, run_n, h->d_tokens);
         acc.launches += 2;
+        if (lanes > 1) B2_CUDA_OK(cudaEventRecord(h->ev_run, st));
+        lane1_synced = false;
       }
       ids = h->job_ids + (i0 - run0) * max_len;
       lens = h->job_lens + (i0 - run0);
-    } else {
-      B2_CUDA_OK(cudaMemcpyAsync(h->ids, d_ids_in + i0 * max_len, size_t(B) * max_len * 4,
-                                 cudaMemcpyDeviceToDevice, st));
-      if ((rc = mask_to_lens(st, d_mask_in + i0 * max_len, h->lens, B, max_len))) return rc;
-      sum_lens_kernel<<<1, 256, 0, st>>>(h->lens, B, h->d_tokens);
+    }
+    if (li == 1 && !lane1_synced) {
+      B2_CUDA_OK(cudaStreamWaitEvent(bb.stream, h->ev_run, 0));
+      lane1_synced = true;
+    }
+    if (!d_utf8) {
+      B2_CUDA_OK(cudaMemcpyAsync(bb.ids, d_ids_in + i0 * max_len, size_t(B) * max_len * 4,
+                                 cudaMemcpyDeviceToDevice, bb.stream));
+      if ((rc = mask_to_lens(bb.stream, d_mask_in + i0 * max_len, bb.lens, B, max_len))) return rc;
+      sum_lens_kernel<<<1, 256, 0, bb.stream>>>(bb.lens, B, h->d_tokens);
       acc.launches += 2;
     }
-    int32_t* lab = d_labels ? d_labels + i0 : reinterpret_cast<int32_t*>(h->mask);  // scratch
-    if ((rc = forward_batch(h, ids, lens, B, max_len, topk, d_top_idx + i0 * topk, d_top_score + i0 * topk,
-                            lab, d_logits ? d_logits + i0 * C : nullptr, &acc.launches))) return rc;
+    int32_t* lab = d_labels ? d_labels + i0 : reinterpret_cast<int32_t*>(bb.mask);  // scratch
+    if ((rc = forward_batch(h, bb, ids, lens, B, max_len, topk, d_top_idx + i0 * topk,
+                            d_top_score + i0 * topk, lab, d_logits ? d_logits + i0 * C : nullptr,
+                            &acc.launches))) return rc;
+    if (li == 1) lane1_busy = true;
     if ((rc = flush_profile(h, &acc))) return rc;
     ++batches;
   }
+  if ((rc = join_lane1())) return rc;
   if (d_hist) {
     hist_to_i64_kernel<<<(C + 255) / 256, 256, 0, st>>>(h->hist, d_hist, C);
     acc.launches += 1;
@@ -820,7 +878,8 @@ int b2_create(const b2_config* cfg, b2_handle** out) {
   int rc = B2_OK;
   do {
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&h->ev_begin) != cudaSuccess || cudaEventCreate(&h->ev_end) != cudaSuccess) {
+        cudaEventCreate(&h->ev_begin) != cudaSuccess || cudaEventCreate(&h->ev_end) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_run, cudaEventDisableTiming) != cudaSuccess) {
       set_last_error("b2_create: cannot create stream / events: %s", cudaGetErrorString(cudaGetLastError()));
       rc = B2_ERR_CUDA;
       break;
@@ -864,6 +923,10 @@ void b2_destroy(b2_handle* h) {
   for (cudaEvent_t e : h->events) cudaEventDestroy(e);
   if (h->ev_begin) cudaEventDestroy(h->ev_begin);
   if (h->ev_end) cudaEventDestroy(h->ev_end);
+  if (h->ev_run) cudaEventDestroy(h->ev_run);
+  for (BatchBuffers& L : h->lane)
+    if (L.done) cudaEventDestroy(L.done);
+  if (h->lane[1].stream) cudaStreamDestroy(h->lane[1].stream);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }

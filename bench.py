@@ -237,30 +237,43 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         hist, merged = _shard.reduce_job(d_hist.cpu().numpy(), m, local_rank)
         return m, hist, merged
 
-    eng.set_profiling(True)
-    for i in range(args.warmup):
-        step_device(i)
-    barrier(); torch.cuda.synchronize()
+    # Two passes over the same K steps. Pass 1 is the timed region of `value`: profiling off, as a
+    # caller runs it. Pass 2 repeats the steps with per-launch CUDA events on the library's stream
+    # (b2_set_profiling) for the per-kernel durations behind `roofline` and `kernels`; those events
+    # cost one stream sync per batch and keep both batch lanes on one stream, so they stay out of
+    # pass 1. `--profile-run` (the command ncu wraps) runs pass 2 only.
+    def timed_pass(profile: bool):
+        eng.set_profiling(profile)
+        for i in range(args.warmup):
+            step_device(i)
+        barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        kern, launches, tokens, hist = {}, 0, 0, None
+        t_wall0 = time.perf_counter()
+        e0.record(ext)
+        for i in range(args.steps):
+            m, hist, merged = step_device(args.warmup + i)
+            launches += m["kernel_launches"]
+            tokens += m["tokens"]
+            for k, v in m.get("kernels", {}).items():
+                a = kern.setdefault(k, {"ms": 0.0, "launches": 0})
+                a["ms"] += v["ms"]; a["launches"] += v["launches"]
+        e1.record(ext)
+        barrier(); torch.cuda.synchronize()
+        wall = (time.perf_counter() - t_wall0) * 1e3
+        assert int(hist.sum()) == n * world, "label histogram does not add up to the job's items"
+        return e0.elapsed_time(e1), wall, kern, launches, tokens
+
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kern = {}
-    launches = 0
-    tokens = 0
-    t_wall0 = time.perf_counter()
-    e0.record(ext)
-    for i in range(args.steps):
-        m, hist, merged = step_device(args.warmup + i)
-        launches += m["kernel_launches"]
-        tokens += m["tokens"]
-        for k, v in m.get("kernels", {}).items():
-            a = kern.setdefault(k, {"ms": 0.0, "launches": 0})
-            a["ms"] += v["ms"]; a["launches"] += v["launches"]
-    e1.record(ext)
-    barrier(); torch.cuda.synchronize()
-    wall_ms = (time.perf_counter() - t_wall0) * 1e3
-    dev_ms = e0.elapsed_time(e1)
+    if args.profile_run:
+        dev_ms, wall_ms, kern, launches, tokens = timed_pass(True)
+        prof_ms = dev_ms
+    else:
+        dev_ms, wall_ms, _, launches, tokens = timed_pass(False)
     clocks = sampler.stop() if sampler else None
-    assert int(hist.sum()) == n * world, "label histogram does not add up to the job's items"
+    if not args.profile_run:
+        prof_ms, _, kern, _, _ = timed_pass(True)
+    eng.set_profiling(False)
 
     def max_over_ranks(x: float) -> float:
         if world == 1:
@@ -377,6 +390,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         "peak_source": f"{peaks['source']} bf16_tflops_sustained (kernel timed inside a long step)",
         "flop_per_launch": g_flop / g_n if g_n else None, "avg_launch_ms": g_ms / g_n if g_n else None,
         "launches": g_n, "share_of_step": round(g_ms / (sum(v["ms"] for v in kern.values()) or 1.0), 4),
+        "measured": "per-launch CUDA events on the library's stream (b2_set_profiling) in a second pass over the "
+                    "same K steps; that pass syncs once per batch and runs both batch lanes on one stream, so it is "
+                    f"not the timed region of `value` ({prof_ms / args.steps:.2f} ms per step against {ms_per_step:.2f})",
         # dram__bytes_read + write per launch, mean of the four encoder GEMMs in one ncu --set full
         # capture at T ~ 71K rows per batch (profiles/r01_ncu_gemm2.md); algorithmic bytes are ~equal
         "traffic": 467.8e6, "traffic_source": "profiles/r01_ncu_round_end.md (ncu capture r01d, mean of one layer's 4 GEMM launches)",
