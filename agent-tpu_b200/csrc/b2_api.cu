@@ -1625,6 +1625,22 @@ int b2_csv_classify(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows
 
 }  // extern "C"
 
+// Developer aid (tests/tools): a block of mapped host memory in which the first bounded mbarrier wait
+// that gives up on the current device records itself before it traps — [0] 0xB2B2B2B2 when set,
+// [1] blockDim.x << 32 | blockIdx.x, [2] barrier smem address << 32 | threadIdx.x,
+// [3] gridDim.x << 32 | parity, [4] %globaltimer. Host memory survives the trapped context.
+extern "C" unsigned long long* b2_debug_trap_log(void) {
+  static unsigned long long* host = nullptr;
+  if (!host) {
+    if (cudaHostAlloc(reinterpret_cast<void**>(&host), 64, cudaHostAllocMapped) != cudaSuccess) return nullptr;
+    memset(host, 0, 64);
+  }
+  unsigned long long* dev = nullptr;
+  if (cudaHostGetDevicePointer(reinterpret_cast<void**>(&dev), host, 0) != cudaSuccess) return nullptr;
+  if (b2::gemm_set_trap_log(dev) || b2::gemm2_set_trap_log(dev) || b2::attention_set_trap_log(dev)) return nullptr;
+  return host;
+}
+
 // ================================================================================================
 // b2_tokenize_noalloc — tokenize without allocating device memory
 // ================================================================================================

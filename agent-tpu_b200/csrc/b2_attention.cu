@@ -283,7 +283,10 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       if (my_items > 2) prefetch_item(2);
       if (my_items > 3) prefetch_item(3);
       for (int i = 0; i + 2 < my_items; ++i) {
-        mbar_wait(bar(S_FULL, 0), i & 1);  // Q·Kᵀ(i) done: its Q and K tiles can be overwritten
+        // Q·Kᵀ(i) done: its Q and K tiles can be overwritten. The S buffer is single, its barrier is
+        // not: Q·Kᵀ(i+1) needs nothing from this thread, so with one barrier a late look here could
+        // find it two phases on, wait for Q·Kᵀ(i+2) — and that one needs the tiles loaded below.
+        mbar_wait(bar(S_FULL, i & 1), (i >> 1) & 1);
         load_qk(i + 2);
         mbar_wait(bar(O_FULL, i & 1), (i >> 1) & 1);  // P·V(i) done: so can its V tile
         load_v(i + 2);
@@ -311,7 +314,7 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) umma_bf16(tmem_base, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
-        umma_commit(bar(S_FULL, 0));
+        umma_commit(bar(S_FULL, s));
       };
       if (my_items > 0) issue_s(0);
       for (int i = 0; i < my_items; ++i) {
@@ -378,7 +381,7 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       const int2 md = meta[i];
       const int len = md.x, row0 = md.y;
       const int kv = min(64, max(0, len - 64 * half));  // valid keys in this thread's half row
-      mbar_wait(bar(S_FULL, 0), i & 1);
+      mbar_wait(bar(S_FULL, s), (i >> 1) & 1);
       if (threadIdx.x == 0) stamp(i, 4);
       tc_fence_after();
       float mx = kv > 0 ? softmax_max64(tS + 64 * half, kv) : -INFINITY;
@@ -691,6 +694,11 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
                                                                      static_cast<int>(items), cu);
   }
   B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int attention_set_trap_log(unsigned long long* mapped) {
+  B2_CUDA_OK(cudaMemcpyToSymbol(g_trap_log, &mapped, sizeof(mapped)));
   return B2_OK;
 }
 

@@ -97,10 +97,26 @@ __device__ __forceinline__ void mbar_wait_poll(uint32_t bar, uint32_t parity) {
 // Bounded wait: a pipeline bug must surface as a trapped launch (cudaErrorLaunchFailure on the
 // host), never as a hung GPU. try_wait itself sleeps in hardware for a bounded time per probe,
 // so the bound below is between ~50 ms and a few seconds of wall clock, far beyond any legitimate wait.
+// Developer aid: where a bounded wait gave up. One copy of the pointer per translation unit (set by
+// that unit's *_set_trap_log); it points at mapped host memory, which survives the trapped context.
+static __device__ unsigned long long* g_trap_log = nullptr;
+static __device__ __noinline__ void mbar_wait_timeout(uint32_t bar, uint32_t parity) {
+  unsigned long long* log = g_trap_log;
+  if (log && atomicCAS_system(log, 0ull, 0xB2B2B2B2ull) == 0ull) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    log[1] = (static_cast<unsigned long long>(blockDim.x) << 32) | blockIdx.x;
+    log[2] = (static_cast<unsigned long long>(bar) << 32) | threadIdx.x;
+    log[3] = (static_cast<unsigned long long>(gridDim.x) << 32) | parity;
+    log[4] = t;
+    __threadfence_system();
+  }
+  __trap();
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 22)) __trap();
+    if (++spins > (1u << 22)) mbar_wait_timeout(bar, parity);
   }
 }
 

@@ -70,6 +70,11 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
 void attention_set_trace(unsigned long long* dev_buf);  // developer timeline hook (dev_check)
 void gemm2_set_trace(unsigned long long* dev_buf, int debug_mode = 0);  // same for the pair GEMM
 
+// developer aid: bounded waits that give up record where (b2_common.cuh: mbar_wait_timeout)
+int gemm_set_trap_log(unsigned long long* mapped);
+int gemm2_set_trap_log(unsigned long long* mapped);
+int attention_set_trap_log(unsigned long long* mapped);
+
 // ---- element-wise / row kernels (b2_rows.cu) ---------------------------------------------------
 // out[row] = LayerNorm(word[ids[row]] + pos[row % S] + type[0]) * gamma + beta  -> bf16
 // packed: with lens / cu given, token (b, s) is written to row cu[b] + s and pad positions are skipped.

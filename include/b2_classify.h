@@ -216,6 +216,11 @@ int b2_csv_classify(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows
 int b2_tokenize_noalloc(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
                         int32_t max_len, int32_t* ids, uint8_t* mask);
 
+/* Developer aid, no reference counterpart: 64 bytes of mapped host memory in which the first bounded
+ * pipeline wait that gives up on the calling thread's current device records where it was before the
+ * launch is trapped (layout in csrc/b2_api.cu). Call after b2_create; NULL on failure. */
+unsigned long long* b2_debug_trap_log(void);
+
 #ifdef __cplusplus
 }
 #endif

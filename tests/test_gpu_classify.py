@@ -120,6 +120,50 @@ def test_batch_size_and_order_independence(tiny_model, vocab_path, sentences):
         a.close(); b.close()
 
 
+def test_two_lanes_equal_one_lane_bit_for_bit(tiny_model, vocab_path, sentences, monkeypatch):
+    """Batches alternating between the two buffer sets / streams (default) against B2_ONE_LANE=1, over
+    enough batches that every lane is reused many times, text and ids entry points: identical bits."""
+    from ops import _cuda_runtime as rt
+    texts = sentences[:1500] + ["", "x"] + sentences[1500:2048]
+    two = rt.Engine(tiny_model, vocab_path, max_batch=64, max_len=128)
+    monkeypatch.setenv("B2_ONE_LANE", "1")
+    one = rt.Engine(tiny_model, vocab_path, max_batch=64, max_len=128)
+    monkeypatch.delenv("B2_ONE_LANE")
+    try:
+        assert two.info.activation_bytes > 1.9 * one.info.activation_bytes
+        a = two.classify(texts, 128, 3, want_logits=True)
+        b = one.classify(texts, 128, 3, want_logits=True)
+        for key in ("logits", "top_idx", "top_score", "labels", "histogram"):
+            assert (a[key] == b[key]).all(), key
+        assert a["metrics"]["tokens"] == b["metrics"]["tokens"] and a["metrics"]["batches"] == 33
+        ids, mask, _ = two.tokenize(texts, 128)
+        c = two.classify_ids(ids, mask, 3, want_logits=True)
+        assert (c["logits"] == a["logits"]).all() and (c["histogram"] == a["histogram"]).all()
+        assert c["metrics"]["tokens"] == a["metrics"]["tokens"]
+    finally:
+        two.close(); one.close()
+
+
+def test_million_item_job_properties(base_engine, sentences):
+    """BASELINE config 3 at full size: 1,000,000 items in batches of 1,024 (977 batches over both lanes,
+    31 tokenizer runs). The input repeats a 2,048-sentence block, so must every output."""
+    n, period = 1_000_000, len(sentences)
+    texts = (sentences * (n // period + 1))[:n]
+    out = base_engine.classify(texts, 128, 5)
+    m = out["metrics"]
+    assert m["items"] == n and m["batches"] == 977
+    assert int(out["histogram"].sum()) == n
+    labels = out["labels"]
+    assert (labels == np.tile(labels[:period], n // period + 1)[:n]).all()
+    assert (out["top_idx"] == np.tile(out["top_idx"][:period], (n // period + 1, 1))[:n]).all()
+    assert (out["top_score"] == np.tile(out["top_score"][:period], (n // period + 1, 1))[:n]).all()
+    assert (out["histogram"] == np.bincount(labels, minlength=out["histogram"].size)).all()
+    base = base_engine.classify(sentences, 128, 5)
+    assert (base["labels"] == labels[:period]).all() and (base["top_score"] == out["top_score"][:period]).all()
+    assert m["tokens"] == base["metrics"]["tokens"] * (n // period) + \
+        base_engine.classify(texts[:n % period], 128, 5)["metrics"]["tokens"]
+
+
 def test_packed_rows_equal_padded_rows_bit_for_bit(tiny_model, vocab_path, sentences, monkeypatch):
     """Padding-free token rows (default) against B2_FORCE_PADDED=1: same logits to the last bit."""
     from ops import _cuda_runtime as rt
