@@ -23,7 +23,8 @@ def test_header_declares_the_expected_surface():
     for must in ("b2_create", "b2_destroy", "b2_last_error", "b2_tokenize", "b2_classify_text",
                  "b2_classify_text_device", "b2_classify_ids", "b2_chunk_count", "b2_chunk_bounds",
                  "b2_device_count", "b2_get_device_info", "b2_get_model_info", "b2_set_profiling",
-                 "b2_get_stream"):
+                 "b2_get_stream", "b2_tokenize_noalloc", "b2_csv_open", "b2_csv_close", "b2_csv_header",
+                 "b2_csv_row_spans", "b2_csv_rows_size", "b2_csv_rows_read", "b2_csv_classify"):
         assert must in syms
 
 
@@ -39,6 +40,8 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(rt.ModelInfo) == 12 * 4 + 16 + 8
     assert C.sizeof(rt.Metrics) == 8 + 7 * 8 + 8 + 10 * 8 + 10 * 8
     assert C.sizeof(rt.DeviceInfo) == 128 + 8 + 16
+    # b2_csv_info: 4 x i32, 5 x i64, 2 x i32, 3 x i64, f64, i64, f64
+    assert C.sizeof(rt.CsvInfo) == 16 + 40 + 8 + 24 + 8 + 8 + 8
 
 
 def _no_cuda():
