@@ -157,11 +157,19 @@ def pack_items(items: Sequence[str]) -> Tuple[np.ndarray, np.ndarray]:
 
     The boundary of Python at 1M items is one join and one cumsum, not a per-item ctypes call
     (SURVEY.md §7.2 "Python at the boundary dominates")."""
-    enc = [s.encode("utf-8", "surrogatepass") for s in items]
-    offsets = np.zeros(len(enc) + 1, dtype=np.int64)
-    if enc:
-        np.cumsum(np.fromiter((len(b) for b in enc), dtype=np.int64, count=len(enc)), out=offsets[1:])
-    blob = np.frombuffer(b"".join(enc), dtype=np.uint8) if enc else np.zeros(0, dtype=np.uint8)
+    n = len(items)
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    if not n:
+        return np.zeros(0, dtype=np.uint8), offsets
+    joined = "".join(items)
+    if joined.isascii():  # one encode for the whole job; byte lengths are the character lengths
+        data = joined.encode("ascii")
+        np.cumsum(np.fromiter(map(len, items), dtype=np.int64, count=n), out=offsets[1:])
+    else:
+        enc = [s.encode("utf-8", "surrogatepass") for s in items]
+        np.cumsum(np.fromiter(map(len, enc), dtype=np.int64, count=n), out=offsets[1:])
+        data = b"".join(enc)
+    blob = np.frombuffer(data, dtype=np.uint8) if data else np.zeros(0, dtype=np.uint8)
     return blob, offsets
 
 

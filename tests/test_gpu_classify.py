@@ -164,6 +164,27 @@ def test_million_item_job_properties(base_engine, sentences):
         base_engine.classify(texts[:n % period], 128, 5)["metrics"]["tokens"]
 
 
+def test_long_document_job_properties(tiny_model, vocab_path):
+    """BASELINE config 4's shape (S = 512, streaming attention kernel) over many batches and both
+    lanes: 6,000 documents of 200-510 tokens repeating a 250-document block; outputs must repeat too,
+    and match a one-lane engine bit for bit."""
+    import synth
+    from ops import _cuda_runtime as rt
+    block = synth.SentenceGenerator().sentences(250, min_tokens=200, max_tokens=510)
+    texts = block * 24
+    eng = rt.Engine(tiny_model, vocab_path, max_batch=64, max_len=512)
+    try:
+        out = eng.classify(texts, 512, 3, want_logits=True)
+        assert out["metrics"]["batches"] == 94 and int(out["histogram"].sum()) == len(texts)
+        assert out["metrics"]["tokens"] > 200 * len(texts)
+        assert (out["logits"] == np.tile(out["logits"][:250], (24, 1))).all()
+        assert (out["labels"] == np.tile(out["labels"][:250], 24)).all()
+        ref = eng.classify(block, 512, 3, want_logits=True)
+        assert (ref["logits"] == out["logits"][:250]).all()
+    finally:
+        eng.close()
+
+
 def test_packed_rows_equal_padded_rows_bit_for_bit(tiny_model, vocab_path, sentences, monkeypatch):
     """Padding-free token rows (default) against B2_FORCE_PADDED=1: same logits to the last bit."""
     from ops import _cuda_runtime as rt
