@@ -331,6 +331,28 @@ __device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
   return r;
 }
 
+__device__ __forceinline__ uint64_t fmul2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// gelu_erf on a pair: the same operations in the same order as the scalar version (so the same bits),
+// with the multiplies and fused multiply-adds issued as packed instructions.
+__device__ __forceinline__ void gelu_erf2(float& a, float& b) {
+  const float ca = fminf(fmaxf(a, -8.0f), 8.0f), cb = fminf(fmaxf(b, -8.0f), 8.0f);
+  const uint64_t xc = f32x2(ca, cb);
+  const uint64_t x2 = fmul2(xc, xc);
+  uint64_t p = ffma2(x2, f32x2(0.0010350828524678946f, 0.0010350828524678946f),
+                     f32x2(-0.10690470039844513f, -0.10690470039844513f));
+  p = ffma2(x2, p, f32x2(-2.300978660583496f, -2.300978660583496f));
+  float ta, tb;
+  f32x2_split(fmul2(xc, p), ta, tb);
+  const uint64_t den = fadd2(f32x2(1.0f, 1.0f), f32x2(ex2_approx(ta), ex2_approx(tb)));
+  float da, db;
+  f32x2_split(den, da, db);
+  f32x2_split(fmul2(f32x2(a, b), f32x2(rcp_approx(da), rcp_approx(db))), a, b);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -331,15 +331,16 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
               // acc·r − μ·r·g + c   (the bias slot carries c)
               const float4 g0 = __ldg(reinterpret_cast<const float4*>(ln.g + colc));
               const float4 g1 = __ldg(reinterpret_cast<const float4*>(ln.g + colc + 4));
+              // packed fp32x2: two columns per instruction, same operations and rounding as scalar fmaf
               const float mr = st.x * st.y;
-              v[0] = fmaf(__uint_as_float(r[j * 8 + 0]), st.y, fmaf(-mr, g0.x, b0.x));
-              v[1] = fmaf(__uint_as_float(r[j * 8 + 1]), st.y, fmaf(-mr, g0.y, b0.y));
-              v[2] = fmaf(__uint_as_float(r[j * 8 + 2]), st.y, fmaf(-mr, g0.z, b0.z));
-              v[3] = fmaf(__uint_as_float(r[j * 8 + 3]), st.y, fmaf(-mr, g0.w, b0.w));
-              v[4] = fmaf(__uint_as_float(r[j * 8 + 4]), st.y, fmaf(-mr, g1.x, b1.x));
-              v[5] = fmaf(__uint_as_float(r[j * 8 + 5]), st.y, fmaf(-mr, g1.y, b1.y));
-              v[6] = fmaf(__uint_as_float(r[j * 8 + 6]), st.y, fmaf(-mr, g1.z, b1.z));
-              v[7] = fmaf(__uint_as_float(r[j * 8 + 7]), st.y, fmaf(-mr, g1.w, b1.w));
+              const uint64_t nmr2 = f32x2(-mr, -mr), rs2 = f32x2(st.y, st.y);
+              const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+              const float cc[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+              for (int e = 0; e < 8; e += 2) {
+                const uint64_t t = ffma2(nmr2, f32x2(gg[e], gg[e + 1]), f32x2(cc[e], cc[e + 1]));
+                f32x2_split(ffma2(f32x2_bits(r[j * 8 + e], r[j * 8 + e + 1]), rs2, t), v[e], v[e + 1]);
+              }
             } else {
               v[0] = __uint_as_float(r[j * 8 + 0]) + b0.x;
               v[1] = __uint_as_float(r[j * 8 + 1]) + b0.y;
@@ -377,8 +378,13 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 for (int e = 0; e < 8; ++e) { psum += v[e]; psq = fmaf(v[e], v[e], psq); }
               }
             }
+            if (EPI == GEMM_EPI_BIAS_GELU || EPI == GEMM_EPI_LNIN_GELU) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = epi_act<EPI>(v[e]);
+              for (int e = 0; e < 8; e += 2) gelu_erf2(v[e], v[e + 1]);
+            } else {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = epi_act<EPI>(v[e]);
+            }
             // Rows at or beyond M inside the last row tile are stored too (the TMA store clips at the
             // buffer, not at M). They must stay finite: they are derived from whatever the same rows
             // held before, batch after batch and layer after layer, and once such a feedback loop

@@ -22,7 +22,8 @@ from typing import List, Optional, Sequence, Tuple
 import numpy as np
 
 _PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG_DIR, "csrc", "libb2classify.so")
+# $B2_LIB_PATH: another build of the same library (A/B runs of two kernel versions on one GPU box)
+LIB_PATH = os.environ.get("B2_LIB_PATH") or os.path.join(_PKG_DIR, "csrc", "libb2classify.so")
 UNICODE_TABLE_PATH = os.path.join(_PKG_DIR, "data", "bert_unicode.bin")
 DEFAULT_MODEL_PATH = "/models/model_b200.b2m"
 
