@@ -169,29 +169,6 @@ __device__ __forceinline__ float softmax_exp64_tmem(uint32_t tS_half, int kv, fl
   return sum;
 }
 
-// Same with P going to columns of its own (tP_half) instead of over S; `before_store` runs once, after
-// the first chunk's arithmetic and before the first write (the place to wait for the previous P·V).
-template <typename Hook>
-__device__ __forceinline__ float softmax_exp64_tmem_to(uint32_t tS_half, uint32_t tP_half, int kv, float sl2,
-                                                       float m_new, Hook&& before_store) {
-  const float moff = m_new * sl2;
-  float sum = 0.f;
-#pragma unroll
-  for (int c = 0; c < 2; ++c) {
-    if (c * 32 < kv) {
-      uint32_t v[32];
-      tmem_ld_32x32(tS_half + c * 32, v);
-      tmem_ld_wait();
-      uint32_t packed[16];
-      sum += softmax_exp32_regs(v, kv - c * 32, sl2, moff, packed);
-      if (c == 0) before_store();
-      tmem_st_32x16(tP_half + c * 16, packed);
-    }
-  }
-  tmem_st_wait();
-  return sum;
-}
-
 // P for this thread's half row (up to 64 keys) given the row maximum; returns the half row's sum.
 __device__ __forceinline__ float softmax_exp64(uint32_t tS, int kv, float sl2, float m_new, uint8_t* tile_row,
                                                int r) {
@@ -659,299 +636,6 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
   }
 }
 
-// ================================================================================================
-// S = 256 .. 512, two-pass kernel: one item = (sequence, head, query block), all its key blocks
-// ================================================================================================
-// Pass 1 computes S_j = Q·K_jᵀ for every key block j into two alternating 128-column buffers and the
-// softmax threads only take the row maximum. Pass 2 recomputes S_j (the tensor core has the time),
-// turns it into P_j with the final maximum and accumulates O += P_j·V_j in tensor memory —
-// no running rescale, no O read-out per key block, P never in shared memory, Q loaded once per item.
-// TMEM: pass 1 S buffers [0,128) and [128,256); pass 2 S in [0,128), O in [128,192), P in [192,256) —
-// with P out of S's columns, Q·K_{j+1}ᵀ is issued ahead of P_j·V_j and is ready when the softmax threads
-// come back for it.
-// smem: Q x2 (items alternate), K ring x2, V ring x2, 16 KiB each.
-struct AttItem {
-  int item, h, qb, len, row0, nkb;
-  bool valid;
-};
-__device__ __forceinline__ void att_item_next(AttItem& it, const int32_t* __restrict__ lens,
-                                              const int32_t* __restrict__ cu, int S, int heads, int qblocks,
-                                              int n_items) {
-  for (;;) {
-    it.item += gridDim.x;
-    if (it.item >= n_items) { it.valid = false; return; }
-    int t = it.item;
-    it.qb = t % qblocks; t /= qblocks;
-    it.h = t % heads;
-    const int b = t / heads;
-    int len = lens[b];
-    len = len < 0 ? 0 : (len > S ? S : len);
-    if (it.qb * QB >= len) continue;  // query block of pad rows only
-    it.len = len;
-    it.nkb = (len + KB - 1) / KB;
-    it.row0 = cu ? cu[b] : b * S;
-    return;
-  }
-}
-__device__ __forceinline__ void att_item_init(AttItem& it, const int32_t* __restrict__ lens,
-                                              const int32_t* __restrict__ cu, int S, int heads, int qblocks,
-                                              int n_items) {
-  it.item = static_cast<int>(blockIdx.x) - static_cast<int>(gridDim.x);
-  it.valid = true;
-  att_item_next(it, lens, cu, S, heads, qblocks, n_items);
-}
-
-enum {  // barrier pairs of the two-pass kernel (index = which * 2 + slot)
-  T_Q_FULL = 0, T_Q_EMPTY, T_K_FULL, T_K_EMPTY, T_V_FULL, T_V_EMPTY, T_S1_FULL, T_S1_EMPTY, T_MAX_DONE,
-  T_S2_FULL, T_P_FULL, T_O_FULL, T_O_EMPTY, T_PV_DONE, T_NBARS
-};
-constexpr uint32_t T_OFF_TMEM = OFF_BARS + 8 * 2 * T_NBARS;  // TMEM base address slot
-constexpr uint32_t T_OFF_RED = OFF_BARS + 256;               // float[4][128]
-static_assert(T_OFF_TMEM + 4 <= T_OFF_RED, "two-pass attention: barrier area");
-static_assert(1024 + T_OFF_RED + 4 * 128 * 4 <= ATT_SMEM, "two-pass attention: shared memory");
-
-__global__ void __launch_bounds__(ATT_THREADS, 2)
-attention_twopass_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
-                         const int32_t* __restrict__ lens, int S, int hidden, int heads, int qblocks,
-                         int n_items, const int32_t* __restrict__ cu,
-                         unsigned long long* __restrict__ trace) {
-  // developer timeline (dev_check "att2trace"): softmax thread 0 of CTA 0 logs (code, %globaltimer)
-  // pairs: 1 S1 seen, 2 S1 released, 3 maximum exchanged, 4 S2 seen, 5 P written, 6 O seen, 7 row stored
-  int n_ev = 0;
-  auto ev = [&](int code) {
-    if (trace && blockIdx.x == 0 && threadIdx.x == 0 && n_ev < 512) {
-      unsigned long long t;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-      trace[2 * n_ev] = code;
-      trace[2 * n_ev + 1] = t;
-      ++n_ev;
-    }
-  };
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t bars = base + OFF_BARS;
-  auto bar = [&](int which, int s) { return bars + 8u * (which * 2 + s); };
-  uint8_t* smem_aligned = smem_raw + (base - raw);
-  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_aligned + T_OFF_TMEM);
-  float* red = reinterpret_cast<float*>(smem_aligned + T_OFF_RED);
-  const uint32_t sQ = base, sK = base + 2 * TILE_BYTES, sV = base + 4 * TILE_BYTES;
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  if (threadIdx.x == ATT_SOFTMAX_THREADS) {
-    for (int s = 0; s < 2; ++s) {
-      for (int w : {T_Q_FULL, T_Q_EMPTY, T_K_FULL, T_K_EMPTY, T_V_FULL, T_V_EMPTY, T_S1_FULL, T_S2_FULL, T_O_FULL,
-                    T_PV_DONE})
-        mbar_init(bar(w, s), 1);
-      for (int w : {T_S1_EMPTY, T_MAX_DONE, T_P_FULL, T_O_EMPTY}) mbar_init(bar(w, s), ATT_SOFTMAX_THREADS);
-    }
-    fence_barrier_init();
-  }
-  if (warp == 8) tmem_alloc<256>(base + T_OFF_TMEM);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot_ptr;
-  auto box_of = [](int valid) { return (min(128, valid) + 31) >> 5; };  // 32-row units
-
-  if (warp == 9) {
-    // ===== TMA thread =====
-    if (lane == 0) {
-      AttItem it;
-      att_item_init(it, lens, cu, S, heads, qblocks, n_items);
-      uint32_t ic = 0, kc = 0, vc = 0;
-      auto load_k = [&](int j) {
-        const int s = kc & 1, kbox = box_of(it.len - j * KB);
-        mbar_wait(bar(T_K_EMPTY, s), ((kc >> 1) & 1) ^ 1u);
-        mbar_expect_tx(bar(T_K_FULL, s), kbox * 32 * 128);
-        tma_load_2d(sK + s * TILE_BYTES, &maps.m[kbox - 1], bar(T_K_FULL, s), hidden + it.h * HD, it.row0 + j * KB);
-        ++kc;
-      };
-      // pull an item's tiles from DRAM into L2 one item ahead of their TMA loads: with two K slots the
-      // pass-1 loop otherwise runs at the pace of one DRAM round trip per key block
-      auto prefetch_item = [&](const AttItem& p) {
-        const int qbox = box_of(p.len - p.qb * QB);
-        tma_prefetch_2d(&maps.m[qbox - 1], p.h * HD, p.row0 + p.qb * QB);
-        for (int j = 0; j < p.nkb; ++j) {
-          const int kbox = box_of(p.len - j * KB);
-          tma_prefetch_2d(&maps.m[kbox - 1], hidden + p.h * HD, p.row0 + j * KB);
-          tma_prefetch_2d(&maps.m[kbox - 1], 2 * hidden + p.h * HD, p.row0 + j * KB);
-        }
-      };
-      if (it.valid) prefetch_item(it);
-      AttItem nx = it;
-      for (; it.valid; it = nx, ++ic) {
-        att_item_next(nx, lens, cu, S, heads, qblocks, n_items);
-        if (nx.valid) prefetch_item(nx);
-        const int qs = ic & 1, qbox = box_of(it.len - it.qb * QB);
-        mbar_wait(bar(T_Q_EMPTY, qs), ((ic >> 1) & 1) ^ 1u);
-        mbar_expect_tx(bar(T_Q_FULL, qs), qbox * 32 * 128);
-        tma_load_2d(sQ + qs * TILE_BYTES, &maps.m[qbox - 1], bar(T_Q_FULL, qs), it.h * HD, it.row0 + it.qb * QB);
-        for (int j = 0; j < it.nkb; ++j) load_k(j);  // pass 1
-        for (int j = 0; j < it.nkb; ++j) {           // pass 2
-          load_k(j);
-          const int s = vc & 1, kbox = box_of(it.len - j * KB);
-          mbar_wait(bar(T_V_EMPTY, s), ((vc >> 1) & 1) ^ 1u);
-          mbar_expect_tx(bar(T_V_FULL, s), kbox * 32 * 128);
-          tma_load_2d(sV + s * TILE_BYTES, &maps.m[kbox - 1], bar(T_V_FULL, s), 2 * hidden + it.h * HD,
-                      it.row0 + j * KB);
-          ++vc;
-        }
-      }
-    }
-  } else if (warp == 8) {
-    // ===== MMA thread =====
-    if (lane == 0) {
-      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
-      AttItem it;
-      att_item_init(it, lens, cu, S, heads, qblocks, n_items);
-      uint32_t ic = 0, kc = 0, vc = 0, s1c = 0, s2c = 0, pc = 0;
-      uint64_t qd = 0;
-      // S = Q·K_jᵀ into TMEM columns [dcol, dcol + 128); frees the K slot when done
-      auto issue_s = [&](int j, uint32_t dcol) {
-        const int s = kc & 1;
-        const uint32_t idesc_s = umma_idesc_bf16(128, box_of(it.len - j * KB) * 32, 0, 0);
-        const uint64_t kd = umma_desc_sw128(sK + s * TILE_BYTES, 16, 1024);
-        mbar_wait(bar(T_K_FULL, s), (kc >> 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k) umma_bf16(tmem_base + dcol, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
-        umma_commit(bar(T_K_EMPTY, s));
-        ++kc;
-      };
-      for (; it.valid; att_item_next(it, lens, cu, S, heads, qblocks, n_items), ++ic) {
-        const int qs = ic & 1;
-        qd = umma_desc_sw128(sQ + qs * TILE_BYTES, 16, 1024);
-        mbar_wait(bar(T_Q_FULL, qs), (ic >> 1) & 1);
-        // the second pass-1 buffer shares its columns with O and P of the previous item
-        if (ic > 0) mbar_wait(bar(T_O_EMPTY, (ic - 1) & 1), ((ic - 1) >> 1) & 1);
-        tc_fence_after();
-        for (int j = 0; j < it.nkb; ++j, ++s1c) {  // pass 1
-          const int sb = s1c & 1;
-          mbar_wait(bar(T_S1_EMPTY, sb), ((s1c >> 1) & 1) ^ 1u);
-          tc_fence_after();
-          issue_s(j, sb * 128);
-          umma_commit(bar(T_S1_FULL, sb));
-        }
-        mbar_wait(bar(T_MAX_DONE, qs), (ic >> 1) & 1);  // every pass-1 read of S is complete
-        tc_fence_after();
-        issue_s(0, 0);
-        umma_commit(bar(T_S2_FULL, s2c & 1));
-        ++s2c;
-        if (it.nkb == 1) umma_commit(bar(T_Q_EMPTY, qs));
-        for (int j = 0; j < it.nkb; ++j, ++pc, ++vc) {  // pass 2
-          const int vs = vc & 1;
-          const int nk16 = box_of(it.len - j * KB) << 1;
-          const uint64_t vd0 = umma_desc_sw128(sV + vs * TILE_BYTES, 8192, 1024);
-          mbar_wait(bar(T_P_FULL, pc & 1), (pc >> 1) & 1);  // P(j) written, S(j) consumed
-          tc_fence_after();
-          if (j + 1 < it.nkb) {
-            issue_s(j + 1, 0);  // first: the softmax threads wait for this one next
-            umma_commit(bar(T_S2_FULL, s2c & 1));
-            ++s2c;
-            if (j + 2 == it.nkb) umma_commit(bar(T_Q_EMPTY, qs));
-          }
-          mbar_wait(bar(T_V_FULL, vs), (vc >> 1) & 1);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            if (k < nk16)
-              umma_bf16_ts(tmem_base + 128, tmem_base + 192 + k * 8, vd0 + k * 128u, idesc_o, (j | k) != 0);
-          }
-          umma_commit(bar(T_V_EMPTY, vs));
-          umma_commit(bar(T_PV_DONE, pc & 1));  // P(j) has been read: P(j+1) may be written
-          if (j + 1 == it.nkb) umma_commit(bar(T_O_FULL, qs));
-        }
-      }
-    }
-  } else {
-    // ===== softmax threads: two per query row =====
-    const int r = threadIdx.x & 127;
-    const int half = threadIdx.x >> 7;  // keys [64*half, +64) of a block, output columns [32*half, +32)
-    const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
-    float* red_max = red;
-    float* red_sum = red + 256;
-    const uint32_t tS = tmem_base + lane_base;
-    AttItem it;
-    att_item_init(it, lens, cu, S, heads, qblocks, n_items);
-    uint32_t ic = 0, s1c = 0, s2c = 0, pc = 0;
-    for (; it.valid; att_item_next(it, lens, cu, S, heads, qblocks, n_items), ++ic) {
-      const int qs = ic & 1;
-      // pass 1: row maximum over all key blocks
-      float mx = -INFINITY;
-      for (int j = 0; j < it.nkb; ++j, ++s1c) {
-        const int sb = s1c & 1;
-        const int kv = min(64, max(0, min(KB, it.len - j * KB) - 64 * half));
-        mbar_wait(bar(T_S1_FULL, sb), (s1c >> 1) & 1);
-        ev(1);
-        tc_fence_after();
-        if (kv > 0) mx = fmaxf(mx, softmax_max64(tS + sb * 128 + 64 * half, kv));
-        tc_fence_before();
-        mbar_arrive(bar(T_S1_EMPTY, sb));
-        ev(2);
-      }
-      red_max[half * 128 + r] = mx;
-      softmax_bar();
-      mx = fmaxf(mx, red_max[(half ^ 1) * 128 + r]);
-      tc_fence_before();
-      mbar_arrive(bar(T_MAX_DONE, qs));
-      ev(3);
-      // pass 2: P_j = exp2((S_j - max)·c) in place, row sum
-      float rowsum = 0.f;
-      for (int j = 0; j < it.nkb; ++j, ++s2c, ++pc) {
-        const int kv = min(64, max(0, min(KB, it.len - j * KB) - 64 * half));
-        mbar_wait(bar(T_S2_FULL, s2c & 1), (s2c >> 1) & 1);
-        ev(4);
-        tc_fence_after();
-        if (kv > 0)
-          rowsum += softmax_exp64_tmem_to(tS + 64 * half, tS + 192 + 32 * half, kv, sl2, mx, [&]() {
-            // the one P buffer is still being read by P·V(j-1) (also across items: pc runs on)
-            if (pc > 0) mbar_wait(bar(T_PV_DONE, (pc - 1) & 1), ((pc - 1) >> 1) & 1);
-          });
-        tc_fence_before();
-        mbar_arrive(bar(T_P_FULL, pc & 1));
-        ev(5);
-      }
-      red_sum[half * 128 + r] = rowsum;
-      softmax_bar();
-      rowsum += red_sum[(half ^ 1) * 128 + r];
-      const float inv = rowsum > 0.f ? 1.0f / rowsum : 0.f;
-      mbar_wait(bar(T_O_FULL, qs), (ic >> 1) & 1);
-      ev(6);
-      tc_fence_after();
-      {
-        uint32_t v[32];
-        tmem_ld_32x32(tS + 128 + half * 32, v);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(bar(T_O_EMPTY, qs));
-        if (r < it.len - it.qb * QB) {
-          __nv_bfloat16* dst = out + static_cast<size_t>(it.row0 + it.qb * QB + r) * hidden + it.h * HD + half * 32;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 w;
-            w.x = pack_bf16x2(__uint_as_float(v[j * 8 + 0]) * inv, __uint_as_float(v[j * 8 + 1]) * inv);
-            w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
-            w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
-            w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + j * 8) = w;
-          }
-        }
-      }
-      ev(7);
-    }
-  }
-
-  __syncwarp();
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 8) {
-    tc_fence_after();
-    tmem_dealloc<256>(tmem_base);
-  }
-}
-
 }  // namespace
 
 // developer hook (dev_check): device buffer of 64 x 8 u64 that CTA 0 of the S=128 kernel fills
@@ -984,8 +668,6 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
                                     ATT_SMEM));
     B2_CUDA_OK(cudaFuncSetAttribute(attention_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     ATT_SMEM));
-    B2_CUDA_OK(cudaFuncSetAttribute(attention_twopass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    ATT_SMEM));
     configured[dev] = true;
   }
   const int heads = hidden / HD, qblocks = S / QB;
@@ -1008,16 +690,8 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
     attention_persist_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(maps, out, lens, S, hidden, heads,
                                                                       static_cast<int>(items), cu, g_att_trace);
   } else {
-    static const bool old_stream = [] {  // developer knob: B2_ATT_STREAM_OLD=1 keeps the one-pass kernel
-      const char* e = getenv("B2_ATT_STREAM_OLD");
-      return e && e[0] == '1';
-    }();
-    if (old_stream)
-      attention_stream_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(maps, out, lens, S, hidden, heads, qblocks,
-                                                                       static_cast<int>(items), cu);
-    else
-      attention_twopass_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(
-          maps, out, lens, S, hidden, heads, qblocks, static_cast<int>(items), cu, g_att_trace);
+    attention_stream_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(maps, out, lens, S, hidden, heads, qblocks,
+                                                                     static_cast<int>(items), cu);
   }
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;

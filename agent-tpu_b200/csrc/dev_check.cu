@@ -366,20 +366,6 @@ int main(int argc, char** argv) {
       }
     }
   }
-  if (!strcmp(what, "att2trace")) {
-    unsigned long long* dtr; CK(cudaMalloc(&dtr, 512 * 16)); CK(cudaMemset(dtr, 0, 512 * 16));
-    check_attention(256, 512, 768, {512, 300}, false);  // warm
-    attention_set_trace(dtr);
-    check_attention(256, 512, 768, {512, 300}, false);
-    attention_set_trace(nullptr);
-    std::vector<unsigned long long> tr(1024);
-    CK(cudaMemcpy(tr.data(), dtr, tr.size() * 8, cudaMemcpyDeviceToHost));
-    printf("two-pass attention, softmax thread 0 of CTA 0: code @ns since first event "
-           "(1 S1 seen, 2 S1 released, 3 max exchanged, 4 S2 seen, 5 P written, 6 O seen, 7 stored)\n");
-    for (int i = 0; i < 160 && tr[2 * i]; ++i)
-      printf("%llu@%lld%s", tr[2 * i], (long long)(tr[2 * i + 1] - tr[1]), (tr[2 * i] == 7) ? "\n" : "  ");
-    printf("\n");
-  }
   if (!strcmp(what, "atttrace")) {
     unsigned long long* dtr; CK(cudaMalloc(&dtr, 64 * 8 * 8)); CK(cudaMemset(dtr, 0, 64 * 8 * 8));
     check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, false);   // warm
