@@ -363,13 +363,17 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       tmem_ld_wait();
       if (write_row) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint4 w;
-          w.x = pack_bf16x2(__uint_as_float(v[j * 8 + 0]) * inv, __uint_as_float(v[j * 8 + 1]) * inv);
-          w.y = pack_bf16x2(__uint_as_float(v[j * 8 + 2]) * inv, __uint_as_float(v[j * 8 + 3]) * inv);
-          w.z = pack_bf16x2(__uint_as_float(v[j * 8 + 4]) * inv, __uint_as_float(v[j * 8 + 5]) * inv);
-          w.w = pack_bf16x2(__uint_as_float(v[j * 8 + 6]) * inv, __uint_as_float(v[j * 8 + 7]) * inv);
-          *reinterpret_cast<uint4*>(dst + j * 8) = w;
+        for (int j = 0; j < 4; j += 2) {
+          uint4 w[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int o = (j + u) * 8;
+            w[u].x = pack_bf16x2(__uint_as_float(v[o + 0]) * inv, __uint_as_float(v[o + 1]) * inv);
+            w[u].y = pack_bf16x2(__uint_as_float(v[o + 2]) * inv, __uint_as_float(v[o + 3]) * inv);
+            w[u].z = pack_bf16x2(__uint_as_float(v[o + 4]) * inv, __uint_as_float(v[o + 5]) * inv);
+            w[u].w = pack_bf16x2(__uint_as_float(v[o + 6]) * inv, __uint_as_float(v[o + 7]) * inv);
+          }
+          st_global_256(dst + j * 8, w[0], w[1]);  // 32-byte aligned: hidden and the head offset are multiples of 64
         }
       }
       if (threadIdx.x == 0) stamp(i, 7);
@@ -613,13 +617,17 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
           __nv_bfloat16* dst =
               out + static_cast<size_t>(it.row0 + it.qb * QB + r) * hidden + it.h * HD + half * 32;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 w;
-            w.x = pack_bf16x2(o[j * 8 + 0] * inv, o[j * 8 + 1] * inv);
-            w.y = pack_bf16x2(o[j * 8 + 2] * inv, o[j * 8 + 3] * inv);
-            w.z = pack_bf16x2(o[j * 8 + 4] * inv, o[j * 8 + 5] * inv);
-            w.w = pack_bf16x2(o[j * 8 + 6] * inv, o[j * 8 + 7] * inv);
-            *reinterpret_cast<uint4*>(dst + j * 8) = w;
+          for (int j = 0; j < 4; j += 2) {
+            uint4 w[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int c = (j + u) * 8;
+              w[u].x = pack_bf16x2(o[c + 0] * inv, o[c + 1] * inv);
+              w[u].y = pack_bf16x2(o[c + 2] * inv, o[c + 3] * inv);
+              w[u].z = pack_bf16x2(o[c + 4] * inv, o[c + 5] * inv);
+              w[u].w = pack_bf16x2(o[c + 6] * inv, o[c + 7] * inv);
+            }
+            st_global_256(dst + j * 8, w[0], w[1]);
           }
         }
       }

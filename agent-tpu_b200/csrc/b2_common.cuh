@@ -353,6 +353,14 @@ __device__ __forceinline__ void gelu_erf2(float& a, float& b) {
   f32x2_split(fmul2(f32x2(a, b), f32x2(rcp_approx(da), rcp_approx(db))), a, b);
 }
 
+// One 256-bit global store (sm_100: STG.256). With one row per thread a warp's store touches 32
+// different 128-byte lines whatever its width, so twice the width is half the L1 wavefronts.
+__device__ __forceinline__ void st_global_256(void* ptr, const uint4& a, const uint4& b) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(a.x), "r"(a.y),
+               "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
