@@ -35,8 +35,8 @@
 //
 // attention_persist_kernel  S = 128: one item = (sequence, head), one key block.
 // attention_stream_kernel   S = 256..512: one ring step = (sequence, head, query block, key block);
-//                           Q is re-fetched with every key block (an L2 hit; it lets P overlay the
-//                           Q|K tiles exactly as in the one-block kernel) and the softmax threads carry
+//                           Q is re-fetched with every key block (an L2 hit), P goes through shared
+//                           memory over the dead Q|K tiles, and the softmax threads carry
 //                           the running maximum, denominator and f32 output row across the key blocks
 //                           (online softmax); blocks wholly beyond the sequence are skipped.
 //
