@@ -64,3 +64,38 @@ def test_shard_is_inert_without_process_group():
     assert _shard.my_slice(10) == (0, 10, 0, 1)
     h, m = _shard.reduce_job(np.arange(4), {"items": 3})
     assert h.tolist() == [0, 1, 2, 3] and m == {"items": 3}
+
+
+def test_slice_bounds_partition_any_job():
+    """Contiguous slices cover [0, n) exactly once for every job size and rank count, and differ in
+    size by at most one item."""
+    from hypothesis import given, settings, strategies as st
+    from ops import _shard
+
+    @settings(max_examples=200, deadline=None)
+    @given(st.integers(0, 10_000_000), st.integers(1, 64))
+    def check(n, world):
+        edges = [_shard.slice_bounds(n, r, world) for r in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == n
+        assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
+        sizes = [hi - lo for lo, hi in edges]
+        assert min(sizes) >= 0 and max(sizes) - min(sizes) <= 1
+
+    check()
+
+
+def test_pack_items_layout_any_text():
+    """pack_items: UTF-8 bytes back to back, offsets[i+1] - offsets[i] = byte length of item i, for
+    ASCII-only jobs (one encode) and mixed ones alike."""
+    from hypothesis import given, settings, strategies as st
+    from ops._cuda_runtime import pack_items
+
+    @settings(max_examples=200, deadline=None)
+    @given(st.lists(st.text(max_size=40), max_size=30))
+    def check(items):
+        blob, off = pack_items(items)
+        enc = [s.encode("utf-8", "surrogatepass") for s in items]
+        assert blob.tobytes() == b"".join(enc)
+        assert off.tolist() == [0] + list(__import__("itertools").accumulate(len(e) for e in enc))
+
+    check()
