@@ -703,6 +703,8 @@ int classify_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offset
   }
   cudaStream_t st = h->stream;
   KindAcc acc;
+  // a previous job that failed half way may have left work on the second lane's stream
+  if (h->n_lanes > 1) B2_CUDA_OK(cudaStreamSynchronize(h->lane[1].stream));
   B2_CUDA_OK(cudaMemsetAsync(h->hist, 0, size_t(C) * 8, st));
   B2_CUDA_OK(cudaMemsetAsync(h->d_tokens, 0, 8, st));
   B2_CUDA_OK(cudaEventRecord(h->ev_begin, st));
