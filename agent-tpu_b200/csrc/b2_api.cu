@@ -156,6 +156,10 @@ struct b2_handle {
   int n_lanes = 1;
   unsigned long long* hist = nullptr;
   int64_t* d_tokens = nullptr;  // running sum of lens
+  int32_t* d_flag = nullptr;    // lowest row of an ids job whose mask is not a non-empty prefix
+  // developer aid (b2_debug_hidden_states): when set, forward_batch leaves an f32 copy of every
+  // layer's output in dbg_hidden[layer][b][s][:] (one batch only)
+  float* dbg_hidden = nullptr;
   bool packed = true;      // padding-free token rows (B2_FORCE_PADDED=1 turns it off)
   bool pair_gemm = true;   // CTA-pair GEMM for the encoder projections (B2_GEMM_1CTA=1 turns it off)
   // LayerNorm folding (B2_NO_LN_FOLD=1 turns it off): no LayerNorm kernel runs in the encoder; the
@@ -261,8 +265,8 @@ int load_model(b2_handle* h, const char* path) {
     return B2_ERR_FORMAT;
   }
   if (m.hidden == 0 || m.hidden % 128 != 0 || m.hidden > 1024 || m.heads * 64 != m.hidden ||
-      m.intermediate % 8 != 0 || m.layers == 0 || m.num_labels == 0 || m.num_labels > 2048 ||
-      m.type_vocab == 0 || m.vocab_size == 0 || m.kind > 1) {
+      m.intermediate == 0 || m.intermediate % 8 != 0 || m.layers == 0 || m.num_labels == 0 ||
+      m.num_labels > 2048 || m.type_vocab == 0 || m.vocab_size == 0 || m.max_positions == 0 || m.kind > 1) {
     fclose(f);
     set_last_error("model '%s': unsupported geometry (hidden=%u must be a multiple of 128 and <= 1024 "
                    "with head dim 64; heads=%u intermediate=%u labels=%u)",
@@ -273,7 +277,15 @@ int load_model(b2_handle* h, const char* path) {
   int64_t max_n = 0;
   for (const auto& s : specs) max_n = std::max(max_n, s.n);
   float* scratch = nullptr;  // f32 staging for tensors that are stored as bf16
-  B2_CUDA_OK(cudaMalloc(&scratch, max_n * sizeof(float)));
+  {
+    const cudaError_t e = cudaMalloc(&scratch, max_n * sizeof(float));
+    if (e != cudaSuccess) {
+      fclose(f);
+      set_last_error("model '%s': cannot allocate %lld bytes of staging: %s", path,
+                     static_cast<long long>(max_n * sizeof(float)), cudaGetErrorString(e));
+      return B2_ERR_CUDA;
+    }
+  }
   std::vector<float> host;
   h->layers.resize(m.layers);
   int rc = B2_OK;
@@ -441,6 +453,7 @@ int alloc_activations(b2_handle* h) {
   int rc;
   auto A = [&](void** p, int64_t bytes) { h->activation_bytes += bytes; return dev_alloc(h, p, bytes); };
   if ((rc = A(reinterpret_cast<void**>(&h->d_tokens), 8))) return rc;
+  if ((rc = A(reinterpret_cast<void**>(&h->d_flag), 8))) return rc;
   h->lane[0].stream = h->stream;
   h->n_lanes = 1;
   if (h->has_model) {
@@ -502,6 +515,10 @@ int forward_batch(b2_handle* h, BatchBuffers& bb, const int32_t* ids, const int3
   if ((rc = embed_layernorm(st, ids, h->word, h->pos, h->type0, h->emb_g, h->emb_b, m.ln_eps, bb.x,
                             M, S, H, m.vocab_size, h->packed ? lens : nullptr, cu))) return rc;
   ++*launches;
+  const size_t dbg_layer = static_cast<size_t>(B) * S * H;  // floats per layer in dbg_hidden
+  if (h->dbg_hidden &&
+      (rc = dump_hidden(st, bb.x, nullptr, nullptr, 0, m.ln_eps, nullptr, nullptr, lens, cu, B, S, H,
+                        h->dbg_hidden))) return rc;
   // encoder projections: CTA-pair kernel when the batch is large enough to fill 74 pairs
   const bool pair = h->pair_gemm && M >= 4096;
   auto gemm = [&](const CUtensorMap& ta, const CUtensorMap& tb1, const CUtensorMap& tb2, const CUtensorMap& tc,
@@ -572,6 +589,7 @@ int forward_batch(b2_handle* h, BatchBuffers& bb, const int32_t* ids, const int3
       mark(h, K_LAYERNORM);
       if ((rc = layernorm_inplace(st, bb.cls, L.ln2_g, L.ln2_b, m.ln_eps, B, H))) return rc;
       *launches += 9;
+      if (h->dbg_hidden && (rc = dump_cls(st, bb.cls, B, S, H, h->dbg_hidden + (l + 1) * dbg_layer))) return rc;
       break;
     }
     if (fold) {
@@ -600,6 +618,9 @@ int forward_batch(b2_handle* h, BatchBuffers& bb, const int32_t* ids, const int3
       if ((rc = gemm_ln(bb.tm_ffn, L.tm2_2, bb.tm_x, L.b2, &bb.tm_y, H, I, GEMM_EPI_LNRES_STATS, f2))) return rc;
       in_part = bb.part_b; in_g = L.ln2_g; in_b = L.ln2_b;
       *launches += 6;
+      if (h->dbg_hidden &&
+          (rc = dump_hidden(st, bb.x, nullptr, in_part, h->part_slots, m.ln_eps, in_g, in_b, lens, cu, B, S, H,
+                            h->dbg_hidden + (l + 1) * dbg_layer))) return rc;
       continue;
     }
     mark(h, K_GEMM_OUT);
@@ -619,6 +640,9 @@ int forward_batch(b2_handle* h, BatchBuffers& bb, const int32_t* ids, const int3
     mark(h, K_LAYERNORM);
     if ((rc = layernorm_inplace(st, bb.x, L.ln2_g, L.ln2_b, m.ln_eps, M, H, m_dev))) return rc;
     *launches += 7;
+    if (h->dbg_hidden &&
+        (rc = dump_hidden(st, bb.x, nullptr, nullptr, 0, m.ln_eps, nullptr, nullptr, lens, cu, B, S, H,
+                          h->dbg_hidden + (l + 1) * dbg_layer))) return rc;
   }
   mark(h, K_POOLER);
   if ((rc = gemm_bf16_tn(st, bb.tm_cls, h->tm_p, bb.pooled, h->bp, nullptr, B, H, H, H, 0,
@@ -728,6 +752,25 @@ int classify_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offset
     lane1_busy = false;
     return B2_OK;
   };
+  if (!d_utf8 && n > 0) {
+    // Pre-tokenised rows: lengths for the whole job first, and with them the check that every mask
+    // row is a non-empty prefix of ones. The encoder only knows sequences as prefixes [0, len) of
+    // their rows, so a mask with a hole, left padding or no token at all would be classified as a
+    // different input without any sign of it; such a job is refused before anything runs.
+    if ((rc = grow(reinterpret_cast<void**>(&h->job_lens), &h->job_lens_cap, size_t(n) * 4))) return rc;
+    B2_CUDA_OK(cudaMemsetAsync(h->d_flag, 0x7f, 4, st));
+    if ((rc = mask_to_lens(st, d_mask_in, h->job_lens, static_cast<int>(n), max_len, h->d_flag))) return rc;
+    sum_lens_kernel<<<1, 1024, 0, st>>>(h->job_lens, static_cast<int>(n), h->d_tokens);
+    acc.launches += 2;
+    int32_t bad = 0;
+    B2_CUDA_OK(cudaMemcpyAsync(&bad, h->d_flag, 4, cudaMemcpyDeviceToHost, st));
+    B2_CUDA_OK(cudaStreamSynchronize(st));
+    if (bad >= 0 && bad < n) {
+      set_last_error("classify: mask row %d is not a non-empty prefix of ones (1..10..0); masks with holes, "
+                     "left padding or no token are not supported", bad);
+      return B2_ERR_ARG;
+    }
+  }
   if (!d_utf8 && lanes > 1) B2_CUDA_OK(cudaEventRecord(h->ev_run, st));  // staged ids, cleared counters
   bool lane1_synced = false;  // lane 1 has waited on ev_run since it was last recorded
   // labels are needed for the histogram even when the caller does not want them
@@ -757,11 +800,8 @@ int classify_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_offset
       lane1_synced = true;
     }
     if (!d_utf8) {
-      B2_CUDA_OK(cudaMemcpyAsync(bb.ids, d_ids_in + i0 * max_len, size_t(B) * max_len * 4,
-                                 cudaMemcpyDeviceToDevice, bb.stream));
-      if ((rc = mask_to_lens(bb.stream, d_mask_in + i0 * max_len, bb.lens, B, max_len))) return rc;
-      sum_lens_kernel<<<1, 256, 0, bb.stream>>>(bb.lens, B, h->d_tokens);
-      acc.launches += 2;
+      ids = d_ids_in + i0 * max_len;
+      lens = h->job_lens + i0;
     }
     int32_t* lab = d_labels ? d_labels + i0 : reinterpret_cast<int32_t*>(bb.mask);  // scratch
     if ((rc = forward_batch(h, bb, ids, lens, B, max_len, topk, d_top_idx + i0 * topk,
@@ -829,6 +869,41 @@ int b2_get_device_info(int32_t device, b2_device_info* out) {
   out->cc_major = p.major;
   out->cc_minor = p.minor;
   out->l2_bytes = p.l2CacheSize;
+  return B2_OK;
+}
+
+int b2_get_device_memory(int32_t device, int64_t* free_bytes, int64_t* total_bytes) {
+  const int ndev = b2_device_count();
+  if (device < 0 || device >= ndev) {
+    set_last_error("b2_get_device_memory: device %d is outside [0, %d)", device, ndev);
+    return B2_ERR_ARG;
+  }
+  DeviceGuard guard(device);
+  size_t f = 0, t = 0;
+  B2_CUDA_OK(cudaMemGetInfo(&f, &t));
+  if (free_bytes) *free_bytes = static_cast<int64_t>(f);
+  if (total_bytes) *total_bytes = static_cast<int64_t>(t);
+  return B2_OK;
+}
+
+int b2_get_peer_info(int32_t device, int32_t peer, int32_t* can_access, int32_t* performance_rank,
+                     int32_t* native_atomics) {
+  const int ndev = b2_device_count();
+  if (device < 0 || device >= ndev || peer < 0 || peer >= ndev) {
+    set_last_error("b2_get_peer_info: devices %d, %d are outside [0, %d)", device, peer, ndev);
+    return B2_ERR_ARG;
+  }
+  int ca = 0, pr = 0, na = 0;
+  if (device != peer) {
+    B2_CUDA_OK(cudaDeviceCanAccessPeer(&ca, device, peer));
+    if (ca) {
+      B2_CUDA_OK(cudaDeviceGetP2PAttribute(&pr, cudaDevP2PAttrPerformanceRank, device, peer));
+      B2_CUDA_OK(cudaDeviceGetP2PAttribute(&na, cudaDevP2PAttrNativeAtomicSupported, device, peer));
+    }
+  }
+  if (can_access) *can_access = ca;
+  if (performance_rank) *performance_rank = pr;
+  if (native_atomics) *native_atomics = na;
   return B2_OK;
 }
 
@@ -997,7 +1072,7 @@ int b2_tokenize_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_off
 
 static int stage_text(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
                       int64_t* n_bytes) {
-  if (n < 0 || n > 0x7fffffff || (n > 0 && (!utf8 && offsets[n] > 0)) || !offsets) {
+  if (!offsets || n < 0 || n > 0x7fffffff || (n > 0 && !utf8 && offsets[n] > 0)) {
     set_last_error("text input: n out of range or NULL utf8 / offsets");
     return B2_ERR_ARG;
   }
@@ -1092,13 +1167,11 @@ static int classify_to_host(b2_handle* h, const uint8_t* d_text, const int64_t* 
                             int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
                             float* logits, b2_metrics* metrics, int64_t h2d);
 
-static int classify_host(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, const int32_t* ids,
-                         const uint8_t* mask, int64_t n, int32_t max_len, int32_t topk,
-                         int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
-                         float* logits, b2_metrics* metrics) {
-  if (!h) { set_last_error("classify: NULL handle"); return B2_ERR_ARG; }
-  std::lock_guard<std::mutex> lock(h->mu);
-  DeviceGuard guard(h->device);
+// the caller holds the handle's lock and has made its device current
+static int classify_host_locked(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, const int32_t* ids,
+                                const uint8_t* mask, int64_t n, int32_t max_len, int32_t topk,
+                                int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
+                                float* logits, b2_metrics* metrics) {
   int rc;
   if ((rc = check_len(h, max_len, true))) return rc;
   const int C = h->mh.num_labels;
@@ -1164,6 +1237,17 @@ static int classify_to_host(b2_handle* h, const uint8_t* d_text, const int64_t* 
   return B2_OK;
 }
 
+static int classify_host(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, const int32_t* ids,
+                         const uint8_t* mask, int64_t n, int32_t max_len, int32_t topk,
+                         int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
+                         float* logits, b2_metrics* metrics) {
+  if (!h) { set_last_error("classify: NULL handle"); return B2_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  return classify_host_locked(h, utf8, offsets, ids, mask, n, max_len, topk, top_idx, top_score, labels,
+                              histogram, logits, metrics);
+}
+
 int b2_classify_text(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
                      int32_t max_len, int32_t topk, int32_t* top_idx, float* top_score,
                      int32_t* labels, int64_t* histogram, float* logits, b2_metrics* metrics) {
@@ -1178,6 +1262,35 @@ int b2_classify_ids(b2_handle* h, const int32_t* ids, const uint8_t* mask, int64
                     int64_t* histogram, float* logits, b2_metrics* metrics) {
   return classify_host(h, nullptr, nullptr, ids, mask, n, max_len, topk, top_idx, top_score, labels,
                        histogram, logits, metrics);
+}
+
+int b2_debug_hidden_states(b2_handle* h, const int32_t* ids, const uint8_t* mask, int64_t n, int32_t max_len,
+                           float* hidden, float* logits) {
+  if (!h || !hidden) { set_last_error("b2_debug_hidden_states: NULL handle or output"); return B2_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  int rc;
+  if ((rc = check_len(h, max_len, true))) return rc;
+  if (n < 1 || n > h->max_batch) {
+    set_last_error("b2_debug_hidden_states: n = %lld is outside [1, max_batch = %d] (one batch only)",
+                   static_cast<long long>(n), h->max_batch);
+    return B2_ERR_LIMIT;
+  }
+  const size_t floats = size_t(h->mh.layers + 1) * size_t(n) * max_len * h->mh.hidden;
+  float* d = nullptr;
+  B2_CUDA_OK(cudaMalloc(&d, floats * sizeof(float)));
+  struct Drop {  // whatever happens, the handle goes back to its normal state
+    b2_handle* h; float* d;
+    ~Drop() { h->dbg_hidden = nullptr; cudaFree(d); }
+  } drop{h, d};
+  B2_CUDA_OK(cudaMemsetAsync(d, 0, floats * sizeof(float), h->stream));
+  h->dbg_hidden = d;
+  std::vector<int32_t> top_idx(n);
+  std::vector<float> top_score(n);
+  if ((rc = classify_host_locked(h, nullptr, nullptr, ids, mask, n, max_len, 1, top_idx.data(), top_score.data(),
+                                 nullptr, nullptr, logits, nullptr))) return rc;
+  B2_CUDA_OK(cudaMemcpy(hidden, d, floats * sizeof(float), cudaMemcpyDeviceToHost));
+  return B2_OK;
 }
 
 int b2_chunk_count(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
@@ -1715,6 +1828,25 @@ extern "C" int b2_tokenize_noalloc(b2_handle* h, const uint8_t* utf8, const int6
   if (offsets[0] != 0 || bytes < 0 || (bytes > 0 && !utf8)) {
     set_last_error("b2_tokenize_noalloc: offsets must start at 0 and utf8 must not be NULL");
     return B2_ERR_ARG;
+  }
+  // Every part is held to the block size on its own before the parts are added up, so that no
+  // product or sum of caller-supplied sizes can wrap around and slip under the limit.
+  constexpr int64_t LIMIT = B2_NOALLOC_SCRATCH_BYTES;
+  if (bytes > LIMIT || n > LIMIT / 8 || max_len > LIMIT / 4 || (n > 0 && n > LIMIT / 5 / max_len)) {
+    set_last_error("b2_tokenize_noalloc: job (%lld text bytes, %lld items x max_len %d) cannot fit the fixed "
+                   "block of %d bytes; split the job or use b2_tokenize",
+                   (long long)bytes, (long long)n, max_len, B2_NOALLOC_SCRATCH_BYTES);
+    return B2_ERR_LIMIT;
+  }
+  // The kernel reads item i at bytes [offsets[i], offsets[i+1]) of the staged text: a descending or
+  // overshooting entry would send it outside the text part of the block (n is bounded by the check
+  // above, so this pass is short).
+  for (int64_t i = 0; i < n; ++i) {
+    if (offsets[i] > offsets[i + 1] || offsets[i + 1] > bytes) {
+      set_last_error("b2_tokenize_noalloc: offsets[%lld..%lld] are not non-decreasing within [0, %lld]",
+                     (long long)i, (long long)i + 1, (long long)bytes);
+      return B2_ERR_ARG;
+    }
   }
   // layout of the fixed block: text | offsets | ids | mask, each part 256-byte aligned
   const size_t off_text = 0;

@@ -106,8 +106,18 @@ int classify_head(cudaStream_t stream, const __nv_bfloat16* pooled, int ld_poole
                   const float* bc, int B, int hidden, int C, int topk, float* logits,
                   int32_t* top_idx, float* top_score, int32_t* labels,
                   unsigned long long* histogram);
-// token counts per sequence from the mask: lens[b] = sum(mask[b,:])
-int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B, int S);
+// token counts per sequence from the mask: lens[b] = sum(mask[b,:]). The encoder treats sequence b as
+// the prefix [0, lens[b]) of its row; *bad_row (device, preset to INT_MAX by the caller, may be null)
+// receives the lowest row whose ones are not exactly such a non-empty prefix.
+int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B, int S,
+                 int32_t* bad_row = nullptr);
+// developer aid (b2_debug_hidden_states): f32 copy of a layer's input rows as the consuming kernels
+// see them — (x − μ)·r·γ + β with statistics from `part` (partial sums) or `stats`, identity if both
+// are null — into out[B, S, H] at padded positions; pad positions are left untouched.
+int dump_hidden(cudaStream_t stream, const __nv_bfloat16* x, const float2* stats, const float2* part, int slots,
+                float eps, const float* gamma, const float* beta, const int32_t* lens, const int32_t* cu,
+                int B, int S, int H, float* out);
+int dump_cls(cudaStream_t stream, const __nv_bfloat16* cls, int B, int S, int H, float* out);
 
 // ---- CSV (b2_csv.cu) ------------------------------------------------------------------------------
 // Record splitter with the semantics of Python's csv reader (default dialect) over bytes

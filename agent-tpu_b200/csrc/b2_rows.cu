@@ -282,16 +282,70 @@ __global__ void gather_cls_norm_kernel(const __nv_bfloat16* __restrict__ src, co
   }
 }
 
+// lens[b] = number of ones in mask row b. Every later kernel treats a sequence as the prefix
+// [0, lens[b]) of its row, so a row is only acceptable if its ones ARE that prefix and there is at
+// least one: the lowest offending row number is left in *bad_row (atomicMin; caller presets it high).
 __global__ void mask_to_lens_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ lens,
-                                    int B, int S) {
+                                    int B, int S, int32_t* __restrict__ bad_row) {
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (b >= B) return;
   const int lane = threadIdx.x & 31;
-  int n = 0;
-  for (int s = lane; s < S; s += 32) n += mask[static_cast<size_t>(b) * S + s] != 0;
+  int n = 0, last = -1;
+  for (int s = lane; s < S; s += 32) {
+    if (mask[static_cast<size_t>(b) * S + s] != 0) { ++n; last = s; }
+  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
-  if (lane == 0) lens[b] = n;
+  for (int o = 16; o > 0; o >>= 1) {
+    n += __shfl_xor_sync(0xffffffffu, n, o);
+    last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+  }
+  if (lane == 0) {
+    lens[b] = n;
+    if (bad_row && (n < 1 || last + 1 != n)) atomicMin(bad_row, b);
+  }
+}
+
+// ---- developer aid: hidden states as the consumers see them ----------------------------------------
+// out[(b*S + s)*H + c] = float of the layer input the next kernel would read for token (b, s):
+// (x − μ)·r·γ + β with (μ, r) from finished statistics, from the partial sums (added in slot order,
+// like every production reader), or the identity when x is already normalised. One warp per token.
+__global__ void __launch_bounds__(256)
+dump_hidden_kernel(const __nv_bfloat16* __restrict__ x, const float2* __restrict__ stats,
+                   const float2* __restrict__ part, int slots, float inv_h, float eps,
+                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                   const int32_t* __restrict__ lens, const int32_t* __restrict__ cu, int B, int S, int H,
+                   float* __restrict__ out) {
+  const int pos = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (pos >= B * S) return;
+  const int lane = threadIdx.x & 31;
+  const int b = pos / S, sp = pos - b * S;
+  if (sp >= lens[b]) return;
+  const size_t row = cu ? static_cast<size_t>(cu[b]) + sp : static_cast<size_t>(pos);
+  float mean = 0.f, rstd = 1.f;
+  if (part) {
+    const float2* p = part + row * slots;
+    float s = 0.f, q = 0.f;
+    for (int i = 0; i < slots; ++i) { const float2 v = p[i]; s += v.x; q += v.y; }
+    mean = s * inv_h;
+    rstd = rsqrtf(fmaxf(q * inv_h - mean * mean, 0.f) + eps);
+  } else if (stats) {
+    const float2 st = stats[row];
+    mean = st.x; rstd = st.y;
+  }
+  const __nv_bfloat16* xr = x + row * H;
+  float* o = out + static_cast<size_t>(pos) * H;
+  for (int c = lane; c < H; c += 32) {
+    const float v = (__bfloat162float(xr[c]) - mean) * rstd;
+    o[c] = gamma ? fmaf(v, gamma[c], beta[c]) : v;
+  }
+}
+
+// out[(b*S)*H + c] = float(cls[b*H + c]): the last layer only exists for the [CLS] rows
+__global__ void dump_cls_kernel(const __nv_bfloat16* __restrict__ cls, int B, int S, int H,
+                                float* __restrict__ out) {
+  const int b = blockIdx.x;
+  for (int c = threadIdx.x; c < H; c += blockDim.x)
+    out[static_cast<size_t>(b) * S * H + c] = __bfloat162float(cls[static_cast<size_t>(b) * H + c]);
 }
 
 }  // namespace
@@ -386,9 +440,27 @@ int gather_cls_rows_norm(cudaStream_t stream, const __nv_bfloat16* src, const fl
   return B2_OK;
 }
 
-int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B, int S) {
+int mask_to_lens(cudaStream_t stream, const uint8_t* mask, int32_t* lens, int B, int S, int32_t* bad_row) {
   if (B <= 0) return B2_OK;
-  mask_to_lens_kernel<<<(B + 7) / 8, 256, 0, stream>>>(mask, lens, B, S);
+  mask_to_lens_kernel<<<(B + 7) / 8, 256, 0, stream>>>(mask, lens, B, S, bad_row);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int dump_hidden(cudaStream_t stream, const __nv_bfloat16* x, const float2* stats, const float2* part, int slots,
+                float eps, const float* gamma, const float* beta, const int32_t* lens, const int32_t* cu,
+                int B, int S, int H, float* out) {
+  if (B <= 0) return B2_OK;
+  const int rows = B * S;
+  dump_hidden_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(x, stats, part, slots, 1.0f / H, eps, gamma, beta, lens,
+                                                         cu, B, S, H, out);
+  B2_CUDA_OK(cudaGetLastError());
+  return B2_OK;
+}
+
+int dump_cls(cudaStream_t stream, const __nv_bfloat16* cls, int B, int S, int H, float* out) {
+  if (B <= 0) return B2_OK;
+  dump_cls_kernel<<<B, 256, 0, stream>>>(cls, B, S, H, out);
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;
 }

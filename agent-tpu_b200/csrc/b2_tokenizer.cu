@@ -5,7 +5,7 @@
 // The reference has no tokenizer of this kind: ops/map_tokenize.py:6-9 cuts text into fixed-width
 // chunks (that behaviour is the chunk kernel at the bottom of this file). This kernel is the
 // "WordPiece tokenize-and-pad kernel" of BASELINE.json's north star and is held bit-exact to
-// tokenizers 0.22.2 `BertWordPieceTokenizer` (tests/test_tokenizer_gpu.py).
+// tokenizers 0.22.2 `BertWordPieceTokenizer` (tests/test_gpu_tokenizer.py).
 //
 // Layout of the work: a warp streams its line through a window of <= 320 normalised characters in
 // shared memory. Per window: (1) 32 bytes per step are decoded and normalised in parallel (table

@@ -110,6 +110,10 @@ def load_library():
     lib.b2_device_count.restype = I32
     lib.b2_device_count.argtypes = []
     lib.b2_get_device_info.argtypes = [I32, C.POINTER(DeviceInfo)]
+    lib.b2_get_device_memory.argtypes = [I32, C.POINTER(I64), C.POINTER(I64)]
+    lib.b2_get_device_memory.restype = C.c_int
+    lib.b2_get_peer_info.argtypes = [I32, I32, C.POINTER(I32), C.POINTER(I32), C.POINTER(I32)]
+    lib.b2_get_peer_info.restype = C.c_int
     lib.b2_create.argtypes = [C.POINTER(_Config), C.POINTER(P)]
     lib.b2_destroy.argtypes = [P]
     lib.b2_destroy.restype = None
@@ -132,6 +136,10 @@ def load_library():
     lib.b2_csv_rows_size.argtypes = [P, I64, I64, I32, C.POINTER(I64), C.POINTER(I64)]
     lib.b2_csv_rows_read.argtypes = [P, I64, I64, I32, P, P, P]
     lib.b2_csv_classify.argtypes = [P, I32, I64, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
+    lib.b2_tokenize_noalloc.argtypes = [P, P, P, I64, I32, P, P]
+    lib.b2_tokenize_noalloc.restype = C.c_int
+    lib.b2_debug_hidden_states.argtypes = [P, P, P, I64, I32, P, P]
+    lib.b2_debug_hidden_states.restype = C.c_int
     for name in ("b2_csv_open", "b2_csv_header", "b2_csv_row_spans", "b2_csv_rows_size", "b2_csv_rows_read",
                  "b2_csv_classify"):
         getattr(lib, name).restype = C.c_int
@@ -270,6 +278,32 @@ class Engine:
                                                     _ptr(logits), C.byref(m)))
         return {"top_idx": top_idx, "top_score": top_score, "labels": labels, "histogram": hist,
                 "logits": logits, "metrics": m.as_dict()}
+
+    def debug_hidden_states(self, ids: np.ndarray, mask: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+        """Test aid (b2_debug_hidden_states): one batch of pre-tokenised rows through the production
+        kernels; returns (hidden [layers + 1, n, max_len, H] float32, logits [n, num_labels])."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        mask = np.ascontiguousarray(mask, dtype=np.uint8)
+        if ids.ndim != 2 or mask.shape != ids.shape:
+            raise ValueError("ids and mask must be [n, max_len] arrays of the same shape")
+        n, max_len = ids.shape
+        hidden = np.empty((int(self.info.layers) + 1, n, max_len, int(self.info.hidden)), dtype=np.float32)
+        logits = np.empty((n, int(self.info.num_labels)), dtype=np.float32)
+        _check(self._lib, self._lib.b2_debug_hidden_states(self._h, _ptr(ids), _ptr(mask), n, int(max_len),
+                                                           _ptr(hidden), _ptr(logits)))
+        return hidden, logits
+
+    def tokenize_noalloc(self, blob: np.ndarray, offsets: np.ndarray, max_len: int,
+                         want_mask: bool = True) -> Tuple[np.ndarray, Optional[np.ndarray]]:
+        """b2_tokenize_noalloc: same answers as tokenize_packed, staged in the library's fixed 8 MiB
+        device block instead of buffers that may have to grow — for callers that must not allocate
+        device memory while running. Jobs beyond the block raise B2Error (code 5)."""
+        n = len(offsets) - 1
+        ids = np.empty((n, max_len), dtype=np.int32)
+        mask = np.empty((n, max_len), dtype=np.uint8) if want_mask else None
+        _check(self._lib, self._lib.b2_tokenize_noalloc(self._h, _ptr(blob), _ptr(offsets), n, int(max_len),
+                                                        _ptr(ids), _ptr(mask)))
+        return ids, mask
 
     def classify_device(self, d_text: int, d_offsets: int, n: int, n_bytes: int, max_len: int, topk: int,
                         d_top_idx: int, d_top_score: int, d_labels: int, d_hist: int, d_logits: int = 0) -> dict:
@@ -421,6 +455,29 @@ def device_infos() -> List[dict]:
         out.append({"index": i, "name": d.name.decode("utf-8", "replace"),
                     "total_memory_bytes": int(d.total_memory_bytes), "sm_count": int(d.sm_count),
                     "compute_capability": f"{d.cc_major}.{d.cc_minor}", "l2_bytes": int(d.l2_bytes)})
+    return out
+
+
+def device_memory(device: int = 0) -> Tuple[int, int]:
+    """(free, total) bytes of HBM on `device` right now."""
+    lib = load_library()
+    f, t = C.c_int64(0), C.c_int64(0)
+    _check(lib, lib.b2_get_device_memory(int(device), C.byref(f), C.byref(t)))
+    return int(f.value), int(t.value)
+
+
+def peer_matrix() -> List[List[dict]]:
+    """peer_matrix()[a][b] = {"access", "rank", "atomics"}: how device a reaches device b's memory."""
+    lib = load_library()
+    n = int(lib.b2_device_count())
+    out = []
+    for a in range(n):
+        row = []
+        for b in range(n):
+            ca, pr, na = C.c_int32(0), C.c_int32(0), C.c_int32(0)
+            _check(lib, lib.b2_get_peer_info(a, b, C.byref(ca), C.byref(pr), C.byref(na)))
+            row.append({"access": bool(ca.value), "rank": int(pr.value), "atomics": bool(na.value)})
+        out.append(row)
     return out
 
 

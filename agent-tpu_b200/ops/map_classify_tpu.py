@@ -52,6 +52,15 @@ def _error_envelope(payload: Dict[str, Any]) -> Dict[str, Any]:
     }
 
 
+def _guarded(work):
+    """(result, None) or (None, exception): under torchrun a rank whose slice fails must still reach
+    the job's collective (ops/_shard.py: reduce_job), so the failure is carried there, not raised here."""
+    try:
+        return work(), None
+    except Exception as e:  # noqa: BLE001 - re-raised by reduce_job on every rank
+        return None, e
+
+
 def _run_csv(payload: Dict[str, Any], h, eng, k: int, max_len: int, t0: float) -> Dict[str, Any]:
     """The chained job csv_shard -> map_tokenize -> map_classify in one task: `source_uri` names a CSV
     file, `text_column` (default "text") the column holding the items, `start_row` / `shard_size`
@@ -89,12 +98,13 @@ def _run_csv(payload: Dict[str, Any], h, eng, k: int, max_len: int, t0: float) -
     col = len(names) - 1 - names[::-1].index(column)  # DictReader keeps the last of duplicate names
 
     lo, hi, rank, world = _shard.my_slice(count)
-    out = index.classify(col, first + lo, hi - lo, max_len=max_len, topk=k,
-                         want_logits=bool(payload.get("return_logits")))
-    metrics = dict(out["metrics"])
+    out, failure = _guarded(lambda: index.classify(col, first + lo, hi - lo, max_len=max_len, topk=k,
+                                                   want_logits=bool(payload.get("return_logits"))))
+    metrics = dict(out["metrics"]) if out else {}
     metrics["csv"] = {"bytes": index.n_bytes, "rows": index.rows, "index_gpu_ms": float(index.info.gpu_ms),
                       "index_kernel_launches": int(index.info.kernel_launches)}
-    hist, metrics = _shard.reduce_job(out["histogram"], metrics, eng.device)
+    hist, metrics = _shard.reduce_job(out["histogram"] if out else np.zeros(int(h.output_details[0]["shape"][-1]), np.int64),
+                                      metrics, eng.device, error=failure)
     result = {
         "op": OP_NAME,
         "model_path": h.model_path,
@@ -155,9 +165,10 @@ def run(payload: Dict[str, Any], ctx: Dict[str, Any] = None) -> Dict[str, Any]:
                 raise ValueError("payload.items must be a list of strings")
             texts = ["" if x is None else str(x) for x in items]
             lo, hi, rank, world = _shard.my_slice(len(texts))
-            out = eng.classify(texts[lo:hi], max_len=max_len, topk=k,
-                               want_logits=bool(payload.get("return_logits")))
-            hist, metrics = _shard.reduce_job(out["histogram"], out["metrics"], eng.device)
+            out, failure = _guarded(lambda: eng.classify(texts[lo:hi], max_len=max_len, topk=k,
+                                                         want_logits=bool(payload.get("return_logits"))))
+            hist, metrics = _shard.reduce_job(out["histogram"] if out else np.zeros(n_classes, np.int64),
+                                              out["metrics"] if out else {}, eng.device, error=failure)
             first = _topk_dicts(out["top_idx"][0], out["top_score"][0]) if hi > lo else []
             result = {
                 "op": OP_NAME,

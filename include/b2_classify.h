@@ -84,6 +84,17 @@ const char* b2_last_error(void);
 int32_t b2_device_count(void);
 int b2_get_device_info(int32_t device, b2_device_info* out);
 
+/* Free and total device memory right now (cudaMemGetInfo), so a controller can size `batch` x
+ * `max_len` for this worker. Extends _detect_gpu (worker_sizing.py:164-185), which reports only
+ * memory.total. Either pointer may be NULL. */
+int b2_get_device_memory(int32_t device, int64_t* free_bytes, int64_t* total_bytes);
+/* How `device` reaches `peer`: can_access = 1 when peer memory is directly addressable (NVLink /
+ * NVSwitch or PCIe P2P), performance_rank = the driver's relative rank of that link (lower is
+ * faster; cudaDevP2PAttrPerformanceRank), native_atomics = 1 when atomics work across it (NVLink).
+ * All 0 for device == peer. No reference counterpart (the reference has no multi-device notion). */
+int b2_get_peer_info(int32_t device, int32_t peer, int32_t* can_access, int32_t* performance_rank,
+                     int32_t* native_atomics);
+
 /* Load model + tokenizer onto a device: make_interpreter + allocate_tensors
  * (ops/_tpu_runtime.py:55-56). */
 int b2_create(const b2_config* config, b2_handle** out);
@@ -124,7 +135,11 @@ int b2_classify_text_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* 
                             float* d_logits, b2_metrics* metrics);
 /* Classify n pre-tokenised rows: ids [n, max_len] int32, mask [n, max_len] uint8 (1 = token).
  * This is the v0 contract's `input: list[int]` (ops/map_classify_tpu.CONTRACT.md:7-8,
- * ops/map_classify_tpu.py:61-72) widened to n rows. Host pointers. */
+ * ops/map_classify_tpu.py:61-72) widened to n rows. Host pointers.
+ * Every mask row must be a non-empty prefix of ones followed by zeros (right padding), which is what
+ * b2_tokenize produces: the encoder stores sequence b as rows [0, len_b) only. A row with a hole,
+ * with left padding or without any token is refused with B2_ERR_ARG (the message names the first
+ * such row) before anything is computed — it would otherwise be classified as a different input. */
 int b2_classify_ids(b2_handle* h, const int32_t* ids, const uint8_t* mask, int64_t n, int32_t max_len,
                     int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels,
                     int64_t* histogram, float* logits, b2_metrics* metrics);
@@ -215,6 +230,18 @@ int b2_csv_classify(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows
 #define B2_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
 int b2_tokenize_noalloc(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
                         int32_t max_len, int32_t* ids, uint8_t* mask);
+
+/* Test aid, no reference counterpart (the reference's model is an opaque interpreter.invoke(),
+ * ops/map_classify_tpu.py:72): run ONE batch of n <= max_batch pre-tokenised rows through the
+ * production kernels exactly as b2_classify_ids does and also return every layer's output as the next
+ * kernel reads it, up-cast to float32:
+ *   hidden [layers + 1, n, max_len, hidden]: [0] the embedding output, [l] the output of encoder
+ *          layer l. Pad positions are zero. The last layer is only computed for position 0 of every
+ *          row (nothing else reaches the pooler), so hidden[layers][:, 1:, :] is zero.
+ *   logits [n, num_labels] or NULL.
+ * It allocates and frees its own device buffer per call; not for production use. Host pointers. */
+int b2_debug_hidden_states(b2_handle* h, const int32_t* ids, const uint8_t* mask, int64_t n, int32_t max_len,
+                           float* hidden, float* logits);
 
 /* Developer aid, no reference counterpart: 64 bytes of mapped host memory in which the first bounded
  * pipeline wait that gives up on the calling thread's current device records where it was before the

@@ -19,6 +19,25 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on a B200)")
 
 
+def _cuda_devices() -> int:
+    try:
+        from ops import _cuda_runtime as rt
+        return rt.device_count()
+    except Exception:
+        return 0
+
+
+def pytest_collection_modifyitems(config, items):
+    """A plain `pytest tests/` on a box without a CUDA device (or without the built library) skips the
+    `gpu` tests instead of failing them one by one; `-m gpu` on a GPU box runs them."""
+    if not any("gpu" in it.keywords for it in items) or _cuda_devices() > 0:
+        return
+    skip = pytest.mark.skip(reason="needs a CUDA device and agent-tpu_b200/csrc/libb2classify.so")
+    for it in items:
+        if "gpu" in it.keywords:
+            it.add_marker(skip)
+
+
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN

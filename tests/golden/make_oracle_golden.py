@@ -67,6 +67,32 @@ def main():
             json.dump({"texts": t, "model": mf.config_dict(c), "vocab_sha256": vocab_sha, "max_len": 128}, f,
                       ensure_ascii=False)
         print(name, logits.shape, "labels", np.bincount(logits.argmax(1), minlength=c.num_labels).tolist())
+    # ---- wide-logit variant of the base model -----------------------------------------------------
+    # Random-init BERT-base logits barely move between inputs (per-class std 0.02-0.05 over these
+    # texts), so an absolute 2e-2 tolerance and an arg-max that is nearly constant say little. This
+    # variant keeps the encoder and pooler and replaces the head: Wc' = scale * Wc and
+    # bc' = -Wc' . mean(pooled), which centres every class over the text set, so that logits span
+    # several units and every class wins somewhere. Only scale and bc' are stored (the test rebuilds
+    # the kind-0 model file from them); tolerances scale with `scale`.
+    path = os.path.join(tmp, "base.b2m")
+    c, W = bo.load_model(path)
+    t = EDGE_TEXTS[:8] + sentences[: 256 - 8]
+    ids, mask = bo.tokenize(vocab_path, t, 128)
+    _, hs = bo.forward(c, W, ids, mask, return_hidden=True)
+    import torch
+    x0 = torch.from_numpy(hs[-1][:, 0, :])
+    pooled = torch.tanh(x0 @ W["Wp"].T + W["bp"])
+    centred = (pooled - pooled.mean(0, keepdim=True)) @ W["Wc"].T
+    scale = float(np.float32(4.0 / float(centred.abs().max())))       # largest |logit| becomes ~4
+    Wc2 = (W["Wc"] * np.float32(scale)).contiguous()
+    bc2 = -(Wc2 @ pooled.mean(0))
+    logits = (pooled @ Wc2.T + bc2).numpy().astype(np.float32)
+    wins = np.bincount(logits.argmax(1), minlength=c.num_labels)
+    print("wide: scale %.2f, logits in [%.2f, %.2f], per-class std %.2f..%.2f, wins %s" % (
+        scale, logits.min(), logits.max(), logits.std(0).min(), logits.std(0).max(), wins.tolist()))
+    assert (wins > 0).all() and logits.max() >= 3 and logits.min() <= -3
+    np.savez_compressed(os.path.join(HERE, "classify_wide_golden.npz"), logits=logits, scale=np.float32(scale),
+                        bc=bc2.numpy().astype(np.float32), lens=mask.sum(1).astype(np.int32))
     # S = 512 (long documents) on the tiny model
     path = os.path.join(tmp, "tiny.b2m")
     c, W = bo.load_model(path)

@@ -119,3 +119,56 @@ def test_two_rank_csv_chain(tmp_path):
     import csv as pycsv, io
     rows = list(pycsv.DictReader(io.StringIO(open(path, "rb").read().decode(), newline="")))[3:104]
     assert l0 + l1 == [len(r["text"].encode()) % 4 for r in rows]
+
+
+def _failing_worker(rank, world, port, q):
+    """Rank 1's slice fails; rank 0's is fine. Both must come out of the op with an exception within
+    seconds (the failing rank still joins the all-reduce), not one of them stuck in the collective."""
+    sys.path.insert(0, os.path.join(ROOT, "agent-tpu_b200"))
+    import types
+
+    import torch.distributed as dist
+    from ops import _shard, map_classify_tpu as op
+
+    C = 4
+
+    def classify(texts, max_len=128, topk=5, want_logits=False):
+        if rank == 1:
+            raise RuntimeError("device fault on rank 1")
+        n = len(texts)
+        return {"top_idx": np.zeros((n, topk), np.int32), "top_score": np.zeros((n, topk), np.float32),
+                "labels": np.zeros(n, np.int32), "histogram": np.bincount(np.zeros(n, np.int64), minlength=C),
+                "logits": None, "metrics": {"items": n, "gpu_ms_total": 1.0}}
+
+    engine = types.SimpleNamespace(device=0, classify=classify)
+    handle = types.SimpleNamespace(interpreter=engine, output_details=[{"shape": (1, C)}], model_path="fake.b2m")
+    op.get_cuda_handle = lambda *a, **k: handle
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        try:
+            op.run({"items": ["a", "b", "c", "d"], "allow_fallback": False})
+            q.put((rank, "no exception", ""))
+        except Exception as e:  # noqa: BLE001
+            q.put((rank, type(e).__name__, str(e)))
+        # with the default allow_fallback the same failure becomes the error envelope on every rank
+        env = op.run({"items": ["a", "b", "c", "d"]})
+        q.put((rank, "envelope", env.get("reason", "")))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_one_failing_rank_fails_the_job_on_all_ranks():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_failing_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in range(4))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[0][:2] == (0, "ShardFailed") and "1 of 2 ranks failed" in got[0][2]
+    assert got[1] == (0, "envelope", got[0][2])
+    assert got[2] == (1, "RuntimeError", "device fault on rank 1")
+    assert got[3] == (1, "envelope", "device fault on rank 1")

@@ -62,3 +62,40 @@ def test_noalloc_refuses_jobs_beyond_its_fixed_block(vocab_path, sentences):
         assert (ids == eng.tokenize(ok, 128)[0]).all()
     finally:
         eng.close()
+
+
+def test_noalloc_leaves_device_memory_untouched_and_checks_offsets(vocab_path, sentences):
+    """What the name promises: once the first call on the GPU has looked up the block's address, a
+    call changes the amount of free device memory by nothing — while b2_tokenize on a job larger than
+    any before it has to grow its staging buffers. And because the kernel indexes the shared block
+    with the caller's offsets, offsets that run backwards or past the text are refused up front."""
+    from ops import _cuda_runtime as rt
+    eng = rt.Engine(None, vocab_path, max_batch=1, max_len=128)
+    try:
+        rc, _, _, err = _noalloc(eng, rt, sentences[:8], 128)            # warm: address lookup done
+        assert rc == 0, err
+        free_before, _ = rt.device_memory(eng.device)
+        for texts in (sentences[:3000], sentences[:100], sentences[:3000]):
+            rc, ids, _, err = _noalloc(eng, rt, texts, 128)
+            assert rc == 0, err
+            assert rt.device_memory(eng.device)[0] == free_before
+        eng.tokenize(sentences[:3000], 128)                              # the allocating path, for contrast
+        assert rt.device_memory(eng.device)[0] < free_before
+        # malformed offsets
+        lib = rt.load_library()
+        blob, offsets = rt.pack_items(sentences[:4])
+        out = np.zeros((4, 128), dtype=np.int32)
+        for bad in (offsets[[0, 2, 1, 3, 4]], np.array([0, 5, 10, 10 ** 9, offsets[4]], dtype=np.int64),
+                    offsets + 1):
+            bad = np.ascontiguousarray(bad, dtype=np.int64)
+            rc = lib.b2_tokenize_noalloc(eng.handle, blob.ctypes.data_as(C.c_void_p), bad.ctypes.data_as(C.c_void_p),
+                                         4, 128, out.ctypes.data_as(C.c_void_p), None)
+            assert rc == 1, (rc, lib.b2_last_error())
+        # sizes whose product would wrap a 64-bit sum are refused, not wrapped
+        rc = lib.b2_tokenize_noalloc(eng.handle, blob.ctypes.data_as(C.c_void_p), offsets.ctypes.data_as(C.c_void_p),
+                                     4, 2 ** 31 - 1, out.ctypes.data_as(C.c_void_p), None)
+        assert rc == 5
+        rc, ids, _, err = _noalloc(eng, rt, sentences[:4], 128)          # still healthy
+        assert rc == 0 and (ids == eng.tokenize(sentences[:4], 128)[0]).all()
+    finally:
+        eng.close()
