@@ -1740,6 +1740,63 @@ int b2_csv_classify(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows
 
 }  // extern "C"
 
+// ---- hooks for the multi-device group (b2_group.cu, b2_internal.h) -------------------------------------
+#include "b2_internal.h"
+namespace b2 {
+
+int handle_device(const b2_handle* h) { return h->device; }
+int handle_num_labels(const b2_handle* h) { return h->has_model ? static_cast<int>(h->mh.num_labels) : 0; }
+bool handle_has_model(const b2_handle* h) { return h->has_model; }
+
+int classify_resident_text(b2_handle* h, const uint8_t* d_text, const int64_t* d_off, int64_t n,
+                           int32_t max_len, int32_t topk, int32_t* top_idx, float* top_score,
+                           int32_t* labels, int64_t* histogram, float* logits, b2_metrics* metrics) {
+  std::lock_guard<std::mutex> lock(h->mu);
+  DeviceGuard guard(h->device);
+  int rc;
+  if ((rc = check_len(h, max_len, true))) return rc;
+  const int C = h->mh.num_labels;
+  if (topk < 1 || topk > C) {
+    set_last_error("topk %d is outside [1, num_labels = %d]", topk, C);
+    return B2_ERR_ARG;
+  }
+  if (n < 0 || n > 0x7fffffff || (n > 0 && (!top_idx || !top_score || !d_off || !d_text))) {
+    set_last_error("classify: n out of range or NULL text / offsets / top_idx / top_score");
+    return B2_ERR_ARG;
+  }
+  // a non-null text pointer is what selects the tokenizer path; an empty job never reads through it
+  const uint8_t* text = d_text ? d_text : reinterpret_cast<const uint8_t*>(h->d_tokens);
+  return classify_to_host(h, text, d_off, nullptr, nullptr, n, max_len, topk, top_idx, top_score, labels,
+                          histogram, logits, metrics, 0);
+}
+
+b2_handle* csv_owner(b2_csv* c) { return c ? c->h : nullptr; }
+
+int csv_column_extract(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows, int64_t* n_bytes) {
+  int rc;
+  if ((rc = csv_check_range(c, start_row, n_rows, "b2_group_csv_classify"))) return rc;
+  if (column < 0) { set_last_error("b2_group_csv_classify: column must be >= 0"); return B2_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(c->h->mu);
+  DeviceGuard guard(c->h->device);
+  if ((rc = csv_extract_range(c, start_row, n_rows, column))) return rc;
+  *n_bytes = c->sz_bytes;
+  return B2_OK;
+}
+
+int csv_column_copy_to(b2_csv* c, int dst_device, uint8_t* d_text, int64_t* d_off, int64_t n_rows,
+                       int64_t n_bytes) {
+  std::lock_guard<std::mutex> lock(c->h->mu);
+  DeviceGuard guard(c->h->device);
+  cudaStream_t st = c->h->stream;
+  if (n_bytes)
+    B2_CUDA_OK(cudaMemcpyPeerAsync(d_text, dst_device, c->d_out, c->h->device, size_t(n_bytes), st));
+  B2_CUDA_OK(cudaMemcpyPeerAsync(d_off, dst_device, c->d_fend, c->h->device, size_t(n_rows + 1) * 8, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  return B2_OK;
+}
+
+}  // namespace b2
+
 // Developer aid (tests/tools): a block of mapped host memory in which the first bounded mbarrier wait
 // that gives up on the current device records itself before it traps — [0] 0xB2B2B2B2 when set,
 // [1] blockDim.x << 32 | blockIdx.x, [2] barrier smem address << 32 | threadIdx.x,

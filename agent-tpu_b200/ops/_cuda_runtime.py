@@ -136,6 +136,18 @@ def load_library():
     lib.b2_csv_rows_size.argtypes = [P, I64, I64, I32, C.POINTER(I64), C.POINTER(I64)]
     lib.b2_csv_rows_read.argtypes = [P, I64, I64, I32, P, P, P]
     lib.b2_csv_classify.argtypes = [P, I32, I64, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics)]
+    lib.b2_group_create.argtypes = [C.POINTER(_Config), P, I32, C.POINTER(P)]
+    lib.b2_group_destroy.argtypes = [P]
+    lib.b2_group_destroy.restype = None
+    lib.b2_group_size.argtypes = [P]
+    lib.b2_group_size.restype = I32
+    lib.b2_group_member.argtypes = [P, I32]
+    lib.b2_group_member.restype = P
+    lib.b2_group_info.argtypes = [P, P, I32, C.POINTER(I32), C.POINTER(I64)]
+    lib.b2_group_classify_text.argtypes = [P, P, P, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics), P]
+    lib.b2_group_csv_classify.argtypes = [P, P, I32, I64, I64, I32, I32, P, P, P, P, P, C.POINTER(Metrics), P]
+    for name in ("b2_group_create", "b2_group_info", "b2_group_classify_text", "b2_group_csv_classify"):
+        getattr(lib, name).restype = C.c_int
     lib.b2_tokenize_noalloc.argtypes = [P, P, P, I64, I32, P, P]
     lib.b2_tokenize_noalloc.restype = C.c_int
     lib.b2_debug_hidden_states.argtypes = [P, P, P, I64, I32, P, P]
@@ -340,6 +352,95 @@ class Engine:
         return bounds[:n_chunks]
 
 
+def _hint_nccl() -> None:
+    """Point the library at the libnccl.so.2 that PyTorch ships when the process has not loaded one yet
+    and the caller has not chosen one ($B2_NCCL_PATH): if torch is imported later it then finds its own
+    copy already in place instead of a second, different one."""
+    if os.environ.get("B2_NCCL_PATH"):
+        return
+    import sys
+    for base in sys.path:
+        cand = os.path.join(base, "nvidia", "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            os.environ["B2_NCCL_PATH"] = cand
+            return
+
+
+class EngineGroup(Engine):
+    """One model + tokenizer resident on several GPUs of this box, driven from this one process
+    (b2_group_*): a job's items are cut into contiguous slices, one per device, and the label
+    histogram and counters are summed with one NCCL all-reduce per job. Everything an Engine can do
+    still works and runs on the first device (`handle` is member 0's); `classify*` use all of them."""
+
+    def __init__(self, model_path: str, vocab_path: Optional[str], devices: Optional[Sequence[int]] = None,
+                 max_batch: int = 1024, max_len: int = 128):
+        self._lib = load_library()
+        self._g = C.c_void_p()
+        self._h = C.c_void_p()
+        devs = [int(d) for d in devices] if devices else []
+        if len(devs) != 1:
+            _hint_nccl()
+        cfg = _Config(C.sizeof(_Config), 0, model_path.encode() if model_path else None,
+                      vocab_path.encode() if vocab_path else None,
+                      UNICODE_TABLE_PATH.encode() if vocab_path else None, int(max_batch), int(max_len))
+        arr = (C.c_int32 * len(devs))(*devs) if devs else None
+        _check(self._lib, self._lib.b2_group_create(C.byref(cfg), arr, len(devs), C.byref(self._g)))
+        self.n_devices = int(self._lib.b2_group_size(self._g))
+        self._h = C.c_void_p(self._lib.b2_group_member(self._g, 0))
+        self.info = ModelInfo()
+        _check(self._lib, self._lib.b2_get_model_info(self._h, C.byref(self.info)))
+        out = (C.c_int32 * self.n_devices)()
+        ver = C.c_int32(0)
+        _check(self._lib, self._lib.b2_group_info(self._g, out, self.n_devices, C.byref(ver), None))
+        self.devices = [int(d) for d in out]
+        self.nccl_version = int(ver.value)
+        self.model_path = model_path
+        self.vocab_path = vocab_path
+        self.device = self.devices[0]
+
+    def close(self) -> None:
+        if getattr(self, "_g", None) is not None and self._g.value:
+            self._lib.b2_group_destroy(self._g)     # destroys the member handles too
+            self._g = C.c_void_p()
+            self._h = C.c_void_p()
+
+    @property
+    def group(self) -> C.c_void_p:
+        return self._g
+
+    def member(self, i: int) -> C.c_void_p:
+        return C.c_void_p(self._lib.b2_group_member(self._g, int(i)))
+
+    def allreduces(self) -> int:
+        n = C.c_int64(0)
+        _check(self._lib, self._lib.b2_group_info(self._g, None, 0, None, C.byref(n)))
+        return int(n.value)
+
+    def set_profiling(self, on: bool) -> None:
+        for i in range(self.n_devices):
+            _check(self._lib, self._lib.b2_set_profiling(self.member(i), 1 if on else 0))
+
+    def _group_metrics(self, total: "Metrics", per) -> dict:
+        d = total.as_dict()
+        d["devices"] = list(self.devices)
+        d["per_device"] = [m.as_dict() for m in per]
+        return d
+
+    def classify_packed(self, blob: np.ndarray, offsets: np.ndarray, max_len: int = 128, topk: int = 5,
+                        want_logits: bool = False, outputs=None) -> dict:
+        n = len(offsets) - 1
+        top_idx, top_score, labels, hist, logits = outputs or self._outputs(n, topk, want_logits)
+        m = Metrics(struct_size=C.sizeof(Metrics))
+        per = (Metrics * self.n_devices)()
+        for p in per:
+            p.struct_size = C.sizeof(Metrics)
+        _check(self._lib, self._lib.b2_group_classify_text(self._g, _ptr(blob), _ptr(offsets), n, int(max_len),
+                                                           int(topk), _ptr(top_idx), _ptr(top_score), _ptr(labels),
+                                                           _ptr(hist), _ptr(logits), C.byref(m), per))
+        return {"top_idx": top_idx, "top_score": top_score, "labels": labels, "histogram": hist,
+                "logits": logits, "metrics": self._group_metrics(m, per)}
+
+
 class CsvIndex:
     """A CSV file resident in one engine's HBM with its record index (b2_csv_open): the device-side
     stand-in for the `csv.DictReader` loop of _read_csv_shard (ops/csv_shard.py:9-26)."""
@@ -405,11 +506,25 @@ class CsvIndex:
         """csv -> tokenize -> classify without the text leaving the device (b2_csv_classify)."""
         top_idx, top_score, labels, hist, logits = self._engine._outputs(n_rows, topk, want_logits)
         m = Metrics(struct_size=C.sizeof(Metrics))
-        _check(self._lib, self._lib.b2_csv_classify(self._c, int(column), int(start_row), int(n_rows),
-                                                    int(max_len), int(topk), _ptr(top_idx), _ptr(top_score),
-                                                    _ptr(labels), _ptr(hist), _ptr(logits), C.byref(m)))
+        eng = self._engine
+        if isinstance(eng, EngineGroup):
+            # the file lives on the group's first device; slices of the text column travel to the
+            # other devices peer to peer (b2_group_csv_classify)
+            per = (Metrics * eng.n_devices)()
+            for p in per:
+                p.struct_size = C.sizeof(Metrics)
+            _check(self._lib, self._lib.b2_group_csv_classify(eng.group, self._c, int(column), int(start_row),
+                                                              int(n_rows), int(max_len), int(topk), _ptr(top_idx),
+                                                              _ptr(top_score), _ptr(labels), _ptr(hist),
+                                                              _ptr(logits), C.byref(m), per))
+            metrics = eng._group_metrics(m, per)
+        else:
+            _check(self._lib, self._lib.b2_csv_classify(self._c, int(column), int(start_row), int(n_rows),
+                                                        int(max_len), int(topk), _ptr(top_idx), _ptr(top_score),
+                                                        _ptr(labels), _ptr(hist), _ptr(logits), C.byref(m)))
+            metrics = m.as_dict()
         return {"top_idx": top_idx, "top_score": top_score, "labels": labels, "histogram": hist,
-                "logits": logits, "metrics": m.as_dict()}
+                "logits": logits, "metrics": metrics}
 
 
 @dataclass(frozen=True)
@@ -490,6 +605,26 @@ def _local_device() -> int:
     return 0
 
 
+def job_devices() -> List[int]:
+    """The devices one op call spreads a job over.
+
+    The agent runs tasks inline in one process (app.py:286), so by default that process drives every
+    GPU of the box through an EngineGroup. $B2_DEVICES narrows it ("0,1,2,3", or "all"); a process
+    that was started one-per-GPU (torchrun sets LOCAL_RANK, or $B2_DEVICE is given) keeps to its own
+    device — there the slices and the all-reduce belong to torch.distributed (ops/_shard.py)."""
+    if any(os.environ.get(v, "").strip().lstrip("-").isdigit() for v in ("B2_DEVICE", "LOCAL_RANK")):
+        return [_local_device()]
+    n = device_count()
+    spec = (os.environ.get("B2_DEVICES") or "all").strip().lower()
+    if spec in ("all", "*", ""):
+        return list(range(n))
+    devs = [int(x) for x in spec.replace(" ", "").split(",") if x != ""]
+    bad = [d for d in devs if d < 0 or d >= n]
+    if bad or not devs:
+        raise ValueError(f"B2_DEVICES={spec!r} names devices outside [0, {n})")
+    return devs
+
+
 def get_cuda_handle(model_path: str, vocab_path: Optional[str] = None, max_len: int = 128,
                     max_batch: int = 1024) -> CUDAHandle:
     """Create/reuse the engine for `model_path` (ops/_tpu_runtime.py:34-63).
@@ -518,7 +653,11 @@ def get_cuda_handle(model_path: str, vocab_path: Optional[str] = None, max_len: 
                 _drop_csv_index()
             _ENGINE.close()
             _ENGINE = None
-        eng = Engine(model_path, vocab, device=_local_device(), max_batch=max_batch, max_len=max_len)
+        devs = job_devices()
+        if len(devs) > 1:
+            eng = EngineGroup(model_path, vocab, devices=devs, max_batch=max_batch, max_len=max_len)
+        else:
+            eng = Engine(model_path, vocab, device=devs[0], max_batch=max_batch, max_len=max_len)
         _ENGINE = eng
         _INPUT_DETAILS = [{"index": 0, "shape": (1, int(eng.info.max_len)), "dtype": np.int32}]
         _OUTPUT_DETAILS = [{"index": 0, "shape": (1, int(eng.info.num_labels)), "dtype": np.float32}]

@@ -215,6 +215,49 @@ int b2_csv_classify(b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows
                     int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels, int64_t* histogram,
                     float* logits, b2_metrics* metrics);
 
+/* ---- one job over several GPUs of one box, from one process ----
+ *
+ * The reference's agent runs one task at a time, inline, in one process (app.py:31 MAX_TASKS=1,
+ * app.py:191 takes tasks[0], app.py:286 "run inline"), so the single call it makes — the op's
+ * run(payload) -> this library — has to spread the job over the box's GPUs itself. A group owns one
+ * b2_handle per device. A job's n items are cut into contiguous slices [i*n/W, (i+1)*n/W), one per
+ * device; one host thread per device runs the per-device pipeline of b2_classify_text on its slice
+ * and writes the results into the caller's arrays at the slice's position, so outputs come back in
+ * item order without any gather. The one exchange per job is an NCCL all-reduce (sum) of
+ * int64[num_labels + 8] — label histogram, the additive b2_metrics counters and a failure count — plus
+ * a max-reduce of the device times, over communicators created once with ncclCommInitAll. No
+ * reference counterpart (the reference scales out by running more agents: SURVEY.md section 2.1). */
+typedef struct b2_group b2_group;
+/* config->device is ignored; devices = NULL or n_devices <= 0 takes every CUDA device of the box.
+ * A group of one device needs no NCCL; more than one loads libnccl.so.2 at run time (a copy the
+ * process has already loaded, else $B2_NCCL_PATH, else the linker's search path) and fails with
+ * B2_ERR_IO if there is none. Weights are loaded on all devices side by side. */
+int b2_group_create(const b2_config* config, const int32_t* devices, int32_t n_devices, b2_group** out);
+void b2_group_destroy(b2_group* g);
+int32_t b2_group_size(b2_group* g);
+/* Member i's handle (owned by the group; valid until b2_group_destroy). Every single-device entry
+ * point works on it; b2_csv_open for a group job must use member 0. */
+b2_handle* b2_group_member(b2_group* g, int32_t i);
+/* devices[i] = CUDA ordinal of member i (up to max_devices entries); nccl_version = ncclGetVersion()
+ * or 0 for a group of one; allreduces = NCCL collectives issued so far. Pointers may be NULL. */
+int b2_group_info(b2_group* g, int32_t* devices, int32_t max_devices, int32_t* nccl_version, int64_t* allreduces);
+/* b2_classify_text over the whole group. metrics: job totals (counters summed over devices by the
+ * all-reduce, gpu_ms_total = the slowest device's time, per-kernel times summed); per_device: NULL or
+ * an array of b2_group_size() b2_metrics (struct_size set in each) for the individual devices.
+ * If any device fails, every device still takes part in the all-reduce and the call returns the
+ * first error. Host pointers. */
+int b2_group_classify_text(b2_group* g, const uint8_t* utf8, const int64_t* offsets, int64_t n, int32_t max_len,
+                           int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels,
+                           int64_t* histogram, float* logits, b2_metrics* metrics, b2_metrics* per_device);
+/* b2_csv_classify over the whole group (BASELINE config 5: csv_shard -> map_tokenize -> map_classify
+ * on 8 GPUs with the NCCL histogram reduce). `c` was opened with b2_csv_open on b2_group_member(g, 0):
+ * the file crosses PCIe once, to that device. Member 0 cuts the text column of each slice of rows out
+ * of the indexed file and sends it to the member that classifies it, device to device (NVLink
+ * peer-to-peer where available); the extracted text never visits the host. */
+int b2_group_csv_classify(b2_group* g, b2_csv* c, int32_t column, int64_t start_row, int64_t n_rows,
+                          int32_t max_len, int32_t topk, int32_t* top_idx, float* top_score, int32_t* labels,
+                          int64_t* histogram, float* logits, b2_metrics* metrics, b2_metrics* per_device);
+
 /* Tokenize-and-pad like b2_tokenize, but without allocating device memory during the call.
  * No counterpart in the reference. It exists for callers that are not allowed to ask the CUDA
  * driver for memory once they are running (a worker with a fixed memory budget, a loop that cannot
