@@ -218,7 +218,8 @@ def test_trained_like_layernorm_statistics_folded_and_explicit(vocab_path, work_
     lengths = [1, 2, 64, 127, 128] + list(np.random.default_rng(3).integers(8, 129, 59))
     ids, mask = _rows(lengths, 128, cfg.vocab_size, seed=21)
     ids = np.minimum(ids, cfg.vocab_size - 1)
-    assert float(np.abs(W["l1.ln1_b"].numpy().mean())) > 1.0          # the offsets made it into the file
+    # the offsets made it into the file: layer 0's output LayerNorm carries the common offset -3
+    assert float(W["l0.ln2_b"].numpy().mean()) < -2.0 and float(W["l0.ln1_b"].numpy().mean()) > 1.0
     folded = rt.Engine(path, vocab_path=None, max_batch=64, max_len=128)
     monkeypatch.setenv("B2_NO_LN_FOLD", "1")
     plain = rt.Engine(path, vocab_path=None, max_batch=64, max_len=128)

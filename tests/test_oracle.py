@@ -78,3 +78,13 @@ def test_bf16_emulation_predicts_the_stated_tolerance(base_model, vocab_path, se
     exact = bo.forward(cfg, W, ids, mask)
     emu = bo.forward(cfg, W, ids, mask, emulate_bf16=True)
     assert np.abs(exact - emu).max() < 2e-2
+
+
+def test_chunk_oracle_reproduces_the_reference_map_tokenize(ref_golden):
+    """oracle/chunk_oracle.py (bench.py's B3 baseline) against the outputs recorded from the
+    reference's own ops/map_tokenize.py: identical dictionaries for all recorded payloads."""
+    import chunk_oracle
+    assert len(ref_golden["map_tokenize"]) >= 21
+    for case in ref_golden["map_tokenize"]:
+        assert chunk_oracle.map_tokenize(case["payload"]) == case["result"], case["payload"]
+    assert chunk_oracle.map_tokenize(None) == {"ok": True, "tokens": [], "count": 0, "total_chars": 0}
