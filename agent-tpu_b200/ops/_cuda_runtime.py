@@ -567,10 +567,31 @@ def device_infos() -> List[dict]:
     for i in range(int(lib.b2_device_count())):
         d = DeviceInfo()
         _check(lib, lib.b2_get_device_info(i, C.byref(d)))
-        out.append({"index": i, "name": d.name.decode("utf-8", "replace"),
-                    "total_memory_bytes": int(d.total_memory_bytes), "sm_count": int(d.sm_count),
-                    "compute_capability": f"{d.cc_major}.{d.cc_minor}", "l2_bytes": int(d.l2_bytes)})
+        entry = {"index": i, "name": d.name.decode("utf-8", "replace"),
+                 "total_memory_bytes": int(d.total_memory_bytes), "sm_count": int(d.sm_count),
+                 "compute_capability": f"{d.cc_major}.{d.cc_minor}", "l2_bytes": int(d.l2_bytes)}
+        try:  # what a controller needs to size `batch` x `max_len` for this worker right now
+            free, _total = device_memory(i)
+            entry["free_memory_bytes"] = free
+            entry["classify_limits"] = classify_limits(free)
+        except B2Error:
+            pass
+        out.append(entry)
     return out
+
+
+def interconnect() -> dict:
+    """How the box's GPUs reach each other's memory: the peer matrix (direct access, the driver's link
+    rank, atomics) and two summaries — every pair directly addressable, and every pair with native
+    atomics, which on this hardware means NVLink / NVSwitch rather than PCIe."""
+    m = peer_matrix()
+    n = len(m)
+    pairs = [(a, b) for a in range(n) for b in range(n) if a != b]
+    return {"gpu_count": n,
+            "peer_access": [[bool(m[a][b]["access"]) for b in range(n)] for a in range(n)],
+            "performance_rank": [[int(m[a][b]["rank"]) for b in range(n)] for a in range(n)],
+            "all_to_all_peer_access": bool(pairs) and all(m[a][b]["access"] for a, b in pairs),
+            "nvlink_all_to_all": bool(pairs) and all(m[a][b]["access"] and m[a][b]["atomics"] for a, b in pairs)}
 
 
 def device_memory(device: int = 0) -> Tuple[int, int]:
@@ -594,6 +615,24 @@ def peer_matrix() -> List[List[dict]]:
             row.append({"access": bool(ca.value), "rank": int(pr.value), "atomics": bool(na.value)})
         out.append(row)
     return out
+
+
+def activation_bytes_per_row(hidden: int = 768, intermediate: int = 3072, lanes: int = 2) -> int:
+    """Device bytes one token row of a batch costs a handle (b2_api.cu: alloc_lane): ids + mask, the bf16
+    arrays x / ctx / y [H], qkv [3H], ffn [I], two (mean, rstd) pairs and two sets of H/64 partial sums,
+    times the number of batch lanes. 1,024 x 128 rows of BERT-base: about 4.1 GB."""
+    slots = (hidden + 63) // 64
+    return lanes * (5 + 2 * (3 * hidden + 3 * hidden + intermediate) + 2 * 8 + 2 * 8 * slots)
+
+
+def classify_limits(free_bytes: int, weight_bytes: int = 700 << 20, hidden: int = 768, intermediate: int = 3072) -> dict:
+    """The largest `batch` x `max_len` a new handle fits into `free_bytes` of HBM (weights and a 1 GiB margin
+    set aside), as rows and as the batch it allows at the two padded lengths of BASELINE.json; `batch` is
+    capped at the library's 4,096 items per encoder pass."""
+    per_row = activation_bytes_per_row(hidden, intermediate)
+    rows = max(0, (int(free_bytes) - int(weight_bytes) - (1 << 30)) // per_row)
+    return {"bytes_per_token_row": per_row, "max_token_rows": int(rows),
+            "max_batch_at_128": int(min(4096, rows // 128)), "max_batch_at_512": int(min(4096, rows // 512))}
 
 
 def _local_device() -> int:

@@ -21,6 +21,8 @@ payload, which the lease protocol's max_payload_bytes (app.py:108) could not car
 """
 from __future__ import annotations
 
+import base64
+import os
 import time
 from typing import Any, Dict, List
 
@@ -50,6 +52,68 @@ def _error_envelope(payload: Dict[str, Any]) -> Dict[str, Any]:
         "reason": payload.get("fallback_reason", "CUDA unavailable"),
         "topk": [],
     }
+
+
+def _packed_array(a: np.ndarray) -> Dict[str, Any]:
+    a = np.ascontiguousarray(a)
+    return {"dtype": a.dtype.newbyteorder("<").name, "shape": list(a.shape),
+            "data": base64.b64encode(a.astype(a.dtype.newbyteorder("<"), copy=False).tobytes()).decode("ascii")}
+
+
+def _attach_outputs(result: Dict[str, Any], out: Dict[str, Any], payload: Dict[str, Any], rank: int, world: int) -> None:
+    """Per-item outputs in the form the payload asks for.
+
+    default        `labels` (list[int]); `results` / `logits` lists with return_results / return_logits —
+                   fine for thousands of items, and what round-1 consumers read.
+    result_format  "packed": one base64 string per array (little-endian int32 labels [n], int32 top_index
+                   and float32 top_score [n, k], float32 logits [n, C] on request) under `packed`, so a
+                   million-item result is ~60 MB of text instead of a JSON list of a million numbers and
+                   a million dicts. `unpack_result` turns it back into arrays.
+    result_uri     a path: the same arrays go into that .npz file and the result only names it — the
+                   output-side twin of `source_uri`, for results beyond what the lease protocol's
+                   requests.post(json=...) should carry (app.py:108 max_payload_bytes, app.py:146)."""
+    arrays = {"labels": out["labels"], "top_index": out["top_idx"], "top_score": out["top_score"]}
+    if payload.get("return_logits") and out.get("logits") is not None:
+        arrays["logits"] = out["logits"]
+    uri = payload.get("result_uri")
+    if uri:
+        if not isinstance(uri, str):
+            raise ValueError("payload.result_uri must be a path string")
+        path = uri if world == 1 else f"{uri}.rank{rank}"
+        if not path.endswith(".npz"):
+            path += ".npz"
+        tmp = path + ".tmp.npz"
+        np.savez(tmp, histogram=np.asarray(out["histogram"], dtype=np.int64), **arrays)
+        os.replace(tmp, path)
+        result["result_uri"] = path
+        result["result_bytes"] = os.path.getsize(path)
+        result["result_arrays"] = {k: {"dtype": str(v.dtype), "shape": list(v.shape)} for k, v in arrays.items()}
+        return
+    fmt = payload.get("result_format", "json")
+    if fmt == "packed":
+        result["packed"] = {"encoding": "base64", "byte_order": "little",
+                            **{k: _packed_array(v) for k, v in arrays.items()}}
+        return
+    if fmt != "json":
+        raise ValueError('payload.result_format must be "json" or "packed"')
+    result["labels"] = out["labels"].tolist()
+    if payload.get("return_results"):
+        result["results"] = [{"topk": _topk_dicts(i, s)} for i, s in zip(out["top_idx"], out["top_score"])]
+    if payload.get("return_logits"):
+        result["logits"] = out["logits"].tolist()
+
+
+def unpack_result(result: Dict[str, Any]) -> Dict[str, np.ndarray]:
+    """Arrays of a result produced with result_format "packed" or result_uri (consumer-side helper)."""
+    if "result_uri" in result:
+        with np.load(result["result_uri"]) as z:
+            return {k: z[k] for k in z.files}
+    out = {}
+    for k, v in result["packed"].items():
+        if isinstance(v, dict):
+            out[k] = np.frombuffer(base64.b64decode(v["data"]), dtype=np.dtype(v["dtype"]).newbyteorder("<")
+                                   ).reshape(v["shape"])
+    return out
 
 
 def _guarded(work):
@@ -115,16 +179,12 @@ def _run_csv(payload: Dict[str, Any], h, eng, k: int, max_len: int, t0: float) -
         "end_row": start_row + count,
         "row_count": count,
         "items_count": count,
-        "labels": out["labels"].tolist(),
         "label_histogram": [int(v) for v in hist],
         "metrics": metrics,
     }
     if world > 1:
         result["shard"] = {"rank": rank, "world_size": world, "start": lo, "end": hi}
-    if payload.get("return_results"):
-        result["results"] = [{"topk": _topk_dicts(i, s)} for i, s in zip(out["top_idx"], out["top_score"])]
-    if payload.get("return_logits"):
-        result["logits"] = out["logits"].tolist()
+    _attach_outputs(result, out, payload, rank, world)
     result["elapsed_ms"] = (time.time() - t0) * 1000.0
     return result
 
@@ -176,17 +236,12 @@ def run(payload: Dict[str, Any], ctx: Dict[str, Any] = None) -> Dict[str, Any]:
                 "topk": first,
                 "elapsed_ms": 0.0,
                 "items_count": len(texts),
-                "labels": out["labels"].tolist(),
                 "label_histogram": [int(v) for v in hist],
                 "metrics": metrics,
             }
             if world > 1:
                 result["shard"] = {"rank": rank, "world_size": world, "start": lo, "end": hi}
-            if payload.get("return_results"):
-                result["results"] = [{"topk": _topk_dicts(i, s)}
-                                     for i, s in zip(out["top_idx"], out["top_score"])]
-            if payload.get("return_logits"):
-                result["logits"] = out["logits"].tolist()
+            _attach_outputs(result, out, payload, rank, world)
             result["elapsed_ms"] = (time.time() - t0) * 1000.0
             return result
 

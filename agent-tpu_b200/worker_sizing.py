@@ -134,20 +134,36 @@ def _cuda_devices() -> List[Dict[str, Any]]:
         return []
 
 
+def _cuda_interconnect() -> Dict[str, Any]:
+    """Peer-access / NVLink facts from the CUDA runtime (through the C-ABI library); {} if unavailable."""
+    try:
+        from ops._cuda_runtime import interconnect
+        return interconnect()
+    except Exception:
+        return {}
+
+
 def _detect_gpu() -> Dict[str, Any]:
     if not _nvidia_visible_devices_allows_gpu():
         return dict(_NO_GPU)
-    devices = _cuda_devices() or _parse_nvidia_smi()
+    from_cuda = _cuda_devices()
+    devices = from_cuda or _parse_nvidia_smi()
     if not devices:
         return dict(_NO_GPU)
     biggest = max(int(d.get("total_memory_bytes", 0) or 0) for d in devices)
-    return {
+    gpu = {
         "gpu_present": True,
         "gpu_count": len(devices),
         "vram_gb": round(biggest / float(1024 ** 3), 2) if biggest > 0 else None,
         "devices": devices,
         "max_gpu_workers": len(devices),  # one worker process per GPU (SURVEY.md §8(e))
     }
+    link = _cuda_interconnect() if from_cuda and len(devices) > 1 else None
+    if link and link.get("gpu_count") == len(devices):
+        # beyond the reference's schema (worker_sizing.py:164-185): whether one agent process can spread a
+        # job over all GPUs with device-to-device slices (ops/_cuda_runtime.EngineGroup)
+        gpu["interconnect"] = link
+    return gpu
 
 
 def _detect_tpu() -> Dict[str, Any]:

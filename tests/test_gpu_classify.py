@@ -311,9 +311,25 @@ def test_op_envelope_on_gpu(base_model, vocab_path, clean_env, sentences, golden
     rt.reset_cache()
 
 
-def test_worker_profile_reports_this_gpu(clean_env):
+def test_worker_profile_reports_this_gpu(clean_env, base_engine):
     import worker_sizing as ws
+    from ops import _cuda_runtime as rt
     gpu = ws.build_worker_profile()["gpu"]
     assert gpu["gpu_present"] and gpu["gpu_count"] >= 1 and gpu["max_gpu_workers"] == gpu["gpu_count"]
     d = gpu["devices"][0]
     assert "B200" in d["name"] and d["sm_count"] == 148 and d["total_memory_bytes"] > 150 * 2 ** 30
+    # capacity facts a controller can size `batch` x `max_len` with
+    assert 0 < d["free_memory_bytes"] <= d["total_memory_bytes"]
+    lim = d["classify_limits"]
+    assert lim["max_batch_at_128"] == 4096 and lim["max_batch_at_512"] >= 1024      # > 100 GB free on this box
+    # the per-row figure is the handle's own allocation: 1,024 x 128 rows of BERT-base
+    rows = base_engine.info.max_batch * base_engine.info.max_len
+    assert abs(base_engine.info.activation_bytes - rows * lim["bytes_per_token_row"]) < 0.02 * base_engine.info.activation_bytes
+    if gpu["gpu_count"] > 1:
+        link = gpu["interconnect"]
+        assert link["gpu_count"] == gpu["gpu_count"] and link["all_to_all_peer_access"] and link["nvlink_all_to_all"]
+        assert not any(link["peer_access"][i][i] for i in range(gpu["gpu_count"]))
+    else:
+        assert "interconnect" not in gpu
+    free, total = rt.device_memory(0)
+    assert total == d["total_memory_bytes"] or abs(total - d["total_memory_bytes"]) < 2 ** 30

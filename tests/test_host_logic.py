@@ -99,3 +99,51 @@ def test_pack_items_layout_any_text():
         assert off.tolist() == [0] + list(__import__("itertools").accumulate(len(e) for e in enc))
 
     check()
+
+
+def test_packed_and_file_results_round_trip(tmp_path, monkeypatch):
+    """result_format "packed" / result_uri: the arrays a consumer unpacks are exactly what the default
+    JSON form carries (no GPU: the engine is a stand-in, the op's own marshalling is under test)."""
+    import json
+    import types
+
+    import numpy as np
+    from ops import map_classify_tpu as op
+
+    C, k = 6, 3
+    rng = np.random.default_rng(0)
+
+    def classify(texts, max_len=128, topk=5, want_logits=False):
+        n = len(texts)
+        logits = rng.normal(size=(n, C)).astype(np.float32)
+        order = np.argsort(-logits, axis=1)[:, :topk].astype(np.int32)
+        return {"top_idx": order, "top_score": np.take_along_axis(logits, order, 1), "labels": order[:, 0].copy(),
+                "histogram": np.bincount(order[:, 0], minlength=C).astype(np.int64),
+                "logits": logits if want_logits else None, "metrics": {"items": n, "gpu_ms_total": 1.0}}
+
+    engine = types.SimpleNamespace(device=0, classify=classify)
+    handle = types.SimpleNamespace(interpreter=engine, output_details=[{"shape": (1, C)}], model_path="fake.b2m")
+    monkeypatch.setattr(op, "get_cuda_handle", lambda *a, **kw: handle)
+    items = [f"item {i}" for i in range(50)]
+    rng = np.random.default_rng(0)
+    plain = op.run({"items": items, "topk": k, "return_results": True, "return_logits": True, "allow_fallback": False})
+    rng = np.random.default_rng(0)
+    packed = op.run({"items": items, "topk": k, "result_format": "packed", "return_logits": True,
+                     "allow_fallback": False})
+    rng = np.random.default_rng(0)
+    filed = op.run({"items": items, "topk": k, "result_uri": str(tmp_path / "out"), "allow_fallback": False})
+    json.dumps(packed); json.dumps(filed)                                     # still pure JSON (app.py:146)
+    assert "labels" not in packed and "labels" not in filed
+    assert list(packed.keys())[:4] == ["op", "model_path", "topk", "elapsed_ms"]     # v0 keys stay in front
+    assert packed["topk"] == plain["topk"] and packed["label_histogram"] == plain["label_histogram"]
+    a = op.unpack_result(packed)
+    assert a["labels"].tolist() == plain["labels"] and a["labels"].dtype == np.int32
+    assert a["top_index"].tolist() == [[t["index"] for t in r["topk"]] for r in plain["results"]]
+    assert np.allclose(a["top_score"], [[t["score"] for t in r["topk"]] for r in plain["results"]])
+    assert np.allclose(a["logits"], plain["logits"]) and a["logits"].shape == (50, C)
+    f = op.unpack_result(filed)
+    assert filed["result_uri"].endswith("out.npz") and filed["result_bytes"] > 0
+    assert f["labels"].tolist() == plain["labels"] and f["histogram"].tolist() == plain["label_histogram"]
+    assert "logits" not in f
+    bad = op.run({"items": items, "result_format": "xml"})
+    assert bad["fallback"] == "cpu" and "result_format" in bad["reason"]
