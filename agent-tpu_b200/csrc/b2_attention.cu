@@ -352,9 +352,10 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
     // O(i) is normalised and stored one item late, in the shadow of Q·Kᵀ(i+2): what it needs is kept
     // in registers across the iteration
     float inv_prev = 0.f;
-    bool write_prev = false;
+    bool write_prev = false, live_prev = false;
     __nv_bfloat16* dst_prev = out;
-    auto store_o = [&](int i, float inv, bool write_row, __nv_bfloat16* dst) {
+    auto store_o = [&](int i, float inv, bool write_row, bool live, __nv_bfloat16* dst) {
+      if (!live) return;  // this warp's 32 query rows lie wholly beyond the sequence: nothing to read or store
       mbar_wait(bar(O_FULL, i & 1), (i >> 1) & 1);
       if (threadIdx.x == 0) stamp(i, 6);
       tc_fence_after();
@@ -384,7 +385,13 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       const int h = idx % heads;
       const int2 md = meta[i];
       const int len = md.x, row0 = md.y;
-      const int kv = min(64, max(0, len - 64 * half));  // valid keys in this thread's half row
+      // A warp owns query rows [32·(warp&3), +32). Rows at or beyond the sequence's TMA box hold stale
+      // shared memory and are never stored, so a warp whose rows all lie there skips the TMEM reads,
+      // the exponentials and the P write (its P rows stay whatever they were: P·V's output rows are
+      // independent and those rows are not written either) and only keeps the barriers moving. At the
+      // synthetic corpus's mean length of 70 tokens that is about a third of the softmax work.
+      const bool live = (warp & 3) * 32 < len;
+      const int kv = live ? min(64, max(0, len - 64 * half)) : 0;  // valid keys in this thread's half row
       mbar_wait(bar(S_FULL, s), (i >> 1) & 1);
       if (threadIdx.x == 0) stamp(i, 4);
       tc_fence_after();
@@ -400,14 +407,15 @@ attention_persist_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __
       softmax_bar();
       rowsum += red_sum[(half ^ 1) * 128 + r];
       // the previous item's output, while the tensor core works on S(i+1) and P·V(i)
-      if (i > 0) store_o(i - 1, inv_prev, write_prev, dst_prev);
+      if (i > 0) store_o(i - 1, inv_prev, write_prev, live_prev, dst_prev);
+      live_prev = live;
       inv_prev = rowsum > 0.f ? 1.0f / rowsum : 0.f;
       // rows past the sequence's length are pad (padded layout) or belong to the next sequence
       // (packed layout): never written
       write_prev = r < len;
       dst_prev = out + static_cast<size_t>(row0 + r) * hidden + h * HD + half * 32;
     }
-    if (my_items > 0) store_o(my_items - 1, inv_prev, write_prev, dst_prev);
+    if (my_items > 0) store_o(my_items - 1, inv_prev, write_prev, live_prev, dst_prev);
   }
 
   __syncwarp();
