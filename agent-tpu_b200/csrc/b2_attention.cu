@@ -652,6 +652,332 @@ attention_stream_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __r
   }
 }
 
+
+// ================================================================================================
+// S = 256 .. 512, second design: one CTA per SM, two query blocks of one (sequence, head) in flight
+// ================================================================================================
+// The streaming kernel above is a serial chain per key block — Q·Kᵀ, softmax, P·V, then the softmax
+// threads read O out of tensor memory to rescale it in registers before the next block may start —
+// and runs at ~220 TFLOP/s. This kernel keeps the chain off the tensor core:
+//   * a work item is (sequence, head, PAIR of 128-query blocks). Softmax group g (eight warps, two
+//     threads per query row) owns query block g; the K and V tiles of a key block are loaded once
+//     and used by both groups (half the shared-memory traffic per FLOP);
+//   * the single MMA thread ping-pongs: when P_g(j) is ready it issues P_g(j)·V(j) and, right behind
+//     it, Q_g·K(j+1)ᵀ, so group g's next scores are being computed while the other group is in its
+//     exponentials; the tensor core never waits for a softmax as long as one group is ahead;
+//   * P never touches shared memory (written as packed bf16 over the S columns, A operand of P·V
+//     from tensor memory, as in the S = 128 kernel);
+//   * O stays in tensor memory for the whole item: P·V accumulates across key blocks. The running
+//     maximum is only replaced when a block's maximum exceeds it by more than 2^8 in the exponent
+//     (then the softmax threads scale O and their partial denominators once, in place); otherwise
+//     P is taken relative to the stale maximum, which is exact after the final division by the
+//     denominator accumulated with the same reference and cannot overflow (P <= 2^8);
+//   * Q tiles are double-buffered across items and K/V tiles run through a four-stage ring that the
+//     TMA thread fills across item boundaries, so the next item's first Q·Kᵀ is issued right behind
+//     the last P·V of the current one.
+// Tensor memory (512 columns): S/P of group 0 at [0,128), of group 1 at [128,256), O at [256,320) and
+// [320,384). Per (query pair, key block) the tensor core has 4 x 256 cycles of work and the MUFU
+// 2 x 1,024 cycles of exponentials, so the exponentials bound this kernel at about half the tensor peak.
+constexpr int PAIR_THREADS = 576;  // warps 0-7 softmax group 0, 8-15 group 1, 16 MMA issue, 17 TMA
+constexpr int PAIR_STAGES = 4;     // K/V ring
+constexpr int PAIR_MAX_ITEMS = 1024;
+constexpr uint32_t PAIR_OFF_KV = 4 * TILE_BYTES;  // after Q[2 stages][2 groups]
+constexpr uint32_t PAIR_OFF_BARS = PAIR_OFF_KV + PAIR_STAGES * 2 * TILE_BYTES;
+constexpr uint32_t PAIR_OFF_RED = PAIR_OFF_BARS + 256;             // float [2 groups][2 halves][128], max then sum
+constexpr uint32_t PAIR_OFF_META = PAIR_OFF_RED + 2 * 2 * 2 * 128 * 4;  // int2[PAIR_MAX_ITEMS]: (len, first row)
+constexpr uint32_t PAIR_SMEM = 1024 + PAIR_OFF_META + PAIR_MAX_ITEMS * 8;
+enum { PB_QFULL = 0, PB_QFREE = 2, PB_KFULL = 4, PB_VFULL = 8, PB_KVFREE = 12, PB_SFULL = 16, PB_PFULL = 18,
+       PB_OFULL = 20, PB_TMEM = 22 };
+
+struct PairStep {
+  int i;       // index into this CTA's item table
+  int n_item;  // how many items this CTA has started before this one
+  int j, nkb, h, qp, len, row0;
+  bool valid;
+};
+
+__device__ __forceinline__ void pair_next_item(PairStep& it, const int2* meta, int my_items, int heads, int qpairs) {
+  for (;;) {
+    if (++it.i >= my_items) { it.valid = false; return; }
+    const int2 md = meta[it.i];
+    int t = static_cast<int>(blockIdx.x) + it.i * static_cast<int>(gridDim.x);
+    it.qp = t % qpairs; t /= qpairs;
+    it.h = t % heads;
+    if (it.qp * 2 * QB >= md.x) continue;  // both query blocks beyond the sequence
+    it.len = md.x; it.row0 = md.y;
+    it.nkb = (md.x + KB - 1) / KB;
+    it.j = 0;
+    ++it.n_item;
+    return;
+  }
+}
+__device__ __forceinline__ void pair_next(PairStep& it, const int2* meta, int my_items, int heads, int qpairs) {
+  if (++it.j < it.nkb) return;
+  pair_next_item(it, meta, my_items, heads, qpairs);
+}
+__device__ __forceinline__ void pair_init(PairStep& it, const int2* meta, int my_items, int heads, int qpairs) {
+  it.i = -1; it.n_item = -1; it.j = 0; it.nkb = 0; it.valid = true;
+  pair_next_item(it, meta, my_items, heads, qpairs);
+}
+// query rows of group g's block in this item (<= 0: the group has nothing to do in this item)
+__device__ __forceinline__ int pair_qrows(const PairStep& it, int g) {
+  return min(QB, it.len - (it.qp * 2 + g) * QB);
+}
+
+__global__ void __launch_bounds__(PAIR_THREADS, 1)
+attention_pair_kernel(const __grid_constant__ AttMaps maps, __nv_bfloat16* __restrict__ out,
+                      const int32_t* __restrict__ lens, int S, int hidden, int heads, int qpairs, int n_items,
+                      const int32_t* __restrict__ cu) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bars = base + PAIR_OFF_BARS;
+  auto bar = [&](int which, int s) { return bars + 8u * (which + s); };
+  uint8_t* smem_aligned = smem_raw + (base - raw);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_aligned + PAIR_OFF_BARS + 8 * PB_TMEM);
+  float* red = reinterpret_cast<float*>(smem_aligned + PAIR_OFF_RED);
+  int2* meta = reinterpret_cast<int2*>(smem_aligned + PAIR_OFF_META);
+  auto q_tile = [&](int qs, int g) { return base + static_cast<uint32_t>(qs * 2 + g) * TILE_BYTES; };
+  auto k_tile = [&](int st) { return base + PAIR_OFF_KV + static_cast<uint32_t>(st) * 2 * TILE_BYTES; };
+  auto v_tile = [&](int st) { return k_tile(st) + TILE_BYTES; };
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int my_items = (n_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                       static_cast<int>(gridDim.x);
+  for (int i = threadIdx.x; i < my_items; i += blockDim.x) {
+    const int idx = blockIdx.x + i * gridDim.x;
+    const int b = idx / (heads * qpairs);
+    int len = lens[b];
+    len = len < 0 ? 0 : (len > S ? S : len);
+    meta[i] = make_int2(len, cu ? cu[b] : b * S);
+  }
+  if (threadIdx.x == 16 * 32) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar(PB_QFULL, s), 1);
+      mbar_init(bar(PB_QFREE, s), 1);
+      mbar_init(bar(PB_SFULL, s), 1);
+      mbar_init(bar(PB_PFULL, s), ATT_SOFTMAX_THREADS);
+      mbar_init(bar(PB_OFULL, s), 1);
+    }
+    for (int s = 0; s < PAIR_STAGES; ++s) {
+      mbar_init(bar(PB_KFULL, s), 1);
+      mbar_init(bar(PB_VFULL, s), 1);
+      mbar_init(bar(PB_KVFREE, s), 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 16) tmem_alloc<512>(bars + 8u * PB_TMEM);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 17) {
+    // ===== TMA thread: Q tiles per item, K / V tiles per step, running ahead through the ring =====
+    if (lane == 0) {
+      PairStep ld;
+      pair_init(ld, meta, my_items, heads, qpairs);
+      for (int t = 0; ld.valid; ++t) {
+        const int st = t % PAIR_STAGES;
+        const uint32_t ph = (t / PAIR_STAGES) & 1;
+        if (ld.j == 0) {
+          const int qs = ld.n_item & 1;
+          mbar_wait(bar(PB_QFREE, qs), ((ld.n_item >> 1) & 1) ^ 1u);
+          const int box0 = (pair_qrows(ld, 0) + 31) >> 5;
+          const int rows1 = pair_qrows(ld, 1);
+          const int box1 = rows1 > 0 ? (rows1 + 31) >> 5 : 0;
+          mbar_expect_tx(bar(PB_QFULL, qs), (box0 + box1) * 32 * 128);
+          tma_load_2d(q_tile(qs, 0), &maps.m[box0 - 1], bar(PB_QFULL, qs), ld.h * HD, ld.row0 + ld.qp * 2 * QB);
+          if (box1)
+            tma_load_2d(q_tile(qs, 1), &maps.m[box1 - 1], bar(PB_QFULL, qs), ld.h * HD,
+                        ld.row0 + ld.qp * 2 * QB + QB);
+        }
+        mbar_wait(bar(PB_KVFREE, st), ph ^ 1u);
+        const int kbox = (min(KB, ld.len - ld.j * KB) + 31) >> 5;
+        mbar_expect_tx(bar(PB_KFULL, st), kbox * 32 * 128);
+        tma_load_2d(k_tile(st), &maps.m[kbox - 1], bar(PB_KFULL, st), hidden + ld.h * HD, ld.row0 + ld.j * KB);
+        mbar_expect_tx(bar(PB_VFULL, st), kbox * 32 * 128);
+        tma_load_2d(v_tile(st), &maps.m[kbox - 1], bar(PB_VFULL, st), 2 * hidden + ld.h * HD, ld.row0 + ld.j * KB);
+        pair_next(ld, meta, my_items, heads, qpairs);
+      }
+    }
+  } else if (warp == 16) {
+    // ===== MMA thread =====
+    if (lane == 0) {
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
+      auto kbox_of = [&](const PairStep& it) { return (min(KB, it.len - it.j * KB) + 31) >> 5; };
+      // S_g(step) = Q_g · K(step)ᵀ into columns [128 g, +128)
+      auto issue_qk = [&](const PairStep& it, int t, int g) {
+        const int st = t % PAIR_STAGES;
+        const int qs = it.n_item & 1;
+        if (it.j == 0) mbar_wait(bar(PB_QFULL, qs), (it.n_item >> 1) & 1);
+        mbar_wait(bar(PB_KFULL, st), (t / PAIR_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t idesc_s = umma_idesc_bf16(128, kbox_of(it) * 32, 0, 0);
+        const uint64_t qd = umma_desc_sw128(q_tile(qs, g), 16, 1024);
+        const uint64_t kd = umma_desc_sw128(k_tile(st), 16, 1024);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_bf16(tmem_base + g * 128, qd + 2u * k, kd + 2u * k, idesc_s, k != 0);
+        umma_commit(bar(PB_SFULL, g));
+      };
+      PairStep cur, nxt;
+      pair_init(cur, meta, my_items, heads, qpairs);
+      nxt = cur;
+      if (nxt.valid) pair_next(nxt, meta, my_items, heads, qpairs);
+      uint32_t np[2] = {0, 0};  // P_FULL phases consumed per group
+      if (cur.valid) {
+        issue_qk(cur, 0, 0);
+        if (pair_qrows(cur, 1) > 0) issue_qk(cur, 0, 1);
+      }
+      for (int t = 0; cur.valid; ++t) {
+        const int st = t % PAIR_STAGES;
+        const uint32_t ph = (t / PAIR_STAGES) & 1;
+        const int last_g = pair_qrows(cur, 1) > 0 ? 1 : 0;
+        const int nk16 = kbox_of(cur) << 1;
+        const bool last_block = cur.j + 1 == cur.nkb;
+        // B = V: MN-major, one 128-byte line per key, 16 keys = 2048 bytes (>>4 = 128) per step
+        const uint64_t vd0 = umma_desc_sw128(v_tile(st), 8192, 1024);
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          if (g <= last_g) {
+            // every thread of group g arrives after it has written its part of P_g(step) — and, at the
+            // first block of an item, after its read-out of the previous item's O_g
+            mbar_wait(bar(PB_PFULL, g), np[g] & 1);
+            ++np[g];
+            mbar_wait(bar(PB_VFULL, st), ph);
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              if (k < nk16)
+                umma_bf16_ts(tmem_base + 256 + g * 64, tmem_base + g * 128 + (k >> 2) * 64 + (k & 3) * 8,
+                             vd0 + k * 128u, idesc_o, (cur.j > 0 || k != 0) ? 1u : 0u);
+            }
+            if (last_block) umma_commit(bar(PB_OFULL, g));
+            if (g == last_g) {
+              umma_commit(bar(PB_KVFREE, st));  // K(step) and V(step) have been consumed by both groups
+              if (last_block) umma_commit(bar(PB_QFREE, cur.n_item & 1));
+            }
+          }
+          // right behind it, the same group's scores for the next step (the tensor core executes in
+          // issue order: S_g is overwritten only after P_g·V has consumed it)
+          if (nxt.valid && pair_qrows(nxt, g) > 0) issue_qk(nxt, t + 1, g);
+        }
+        cur = nxt;
+        if (nxt.valid) pair_next(nxt, meta, my_items, heads, qpairs);
+      }
+    }
+  } else {
+    // ===== softmax group g: query block g of every item =====
+    const int g = warp >> 3;
+    const int r = threadIdx.x & 127;          // query row within the block
+    const int half = (threadIdx.x >> 7) & 1;  // keys [64*half, +64) of a key block, output columns [32*half, +32)
+    const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const float sl2 = 0.125f * 1.44269504088896340736f;  // 1/sqrt(64) * log2(e)
+    constexpr float kRescaleAt = 8.0f;                   // exponent (log2) by which a block maximum may exceed the reference
+    float* red_max = red + g * 256;
+    float* red_sum = red + 512 + g * 256;
+    const uint32_t tS = tmem_base + lane_base + g * 128;
+    const uint32_t tO = tmem_base + lane_base + 256 + g * 64 + half * 32;
+    const int group_bar = 1 + g;
+    auto group_sync = [&]() { asm volatile("bar.sync %0, 256;" ::"r"(group_bar) : "memory"); };
+    uint32_t ns = 0, ni = 0;  // S_FULL / O_FULL phases consumed
+    float m_ref = 0.f, l_part = 0.f;
+    PairStep it;
+    pair_init(it, meta, my_items, heads, qpairs);
+    while (it.valid) {
+      const int qrows = pair_qrows(it, g);
+      if (qrows <= 0) {  // this group sits the item out
+        pair_next_item(it, meta, my_items, heads, qpairs);
+        continue;
+      }
+      const bool live = (warp & 3) * 32 < qrows;  // warps whose rows are all pad only keep the barriers moving
+      const int kvalid = min(KB, it.len - it.j * KB);
+      const int kv = live ? min(64, max(0, kvalid - 64 * half)) : 0;
+      mbar_wait(bar(PB_SFULL, g), ns & 1);
+      ++ns;
+      tc_fence_after();
+      float mx = kv > 0 ? softmax_max64(tS + 64 * half, kv) : -INFINITY;
+      red_max[half * 128 + r] = mx;
+      group_sync();
+      mx = fmaxf(mx, red_max[(half ^ 1) * 128 + r]);
+      if (live) {
+        if (it.j == 0) {
+          m_ref = mx;
+          l_part = 0.f;
+        } else if (__any_sync(0xffffffffu, (mx - m_ref) * sl2 > kRescaleAt)) {
+          // S_FULL of this step implies P·V of the previous one has completed (commit covers every
+          // earlier MMA), and P·V of this step waits for our arrival below: O is ours to scale.
+          // The tensor-memory accesses are warp-wide, so the whole warp takes this path as soon as
+          // one of its rows needs it; rows that do not keep their reference (alpha = 1).
+          const bool grow = (mx - m_ref) * sl2 > kRescaleAt;
+          const float alpha = grow ? ex2_approx((m_ref - mx) * sl2) : 1.0f;
+          uint32_t v[32];
+          tmem_ld_32x32(tO, v);
+          tmem_ld_wait();
+          uint32_t lo[16], hi[16];
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            lo[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
+            hi[e] = __float_as_uint(__uint_as_float(v[16 + e]) * alpha);
+          }
+          tmem_st_32x16(tO, lo);
+          tmem_st_32x16(tO + 16, hi);
+          tmem_st_wait();
+          l_part *= alpha;
+          if (grow) m_ref = mx;
+        }
+        if (kv > 0) l_part += softmax_exp64_tmem(tS + 64 * half, kv, sl2, m_ref);
+      }
+      tc_fence_before();
+      mbar_arrive(bar(PB_PFULL, g));
+      if (it.j + 1 == it.nkb) {
+        // last key block: wait for the item's last P·V, normalise, store
+        red_sum[half * 128 + r] = l_part;
+        group_sync();
+        const float l = l_part + red_sum[(half ^ 1) * 128 + r];
+        mbar_wait(bar(PB_OFULL, g), ni & 1);
+        ++ni;
+        tc_fence_after();
+        if (live) {
+          uint32_t v[32];
+          tmem_ld_32x32(tO, v);
+          tmem_ld_wait();
+          if (r < qrows) {
+            const float inv = l > 0.f ? 1.0f / l : 0.f;
+            __nv_bfloat16* dst = out + static_cast<size_t>(it.row0 + (it.qp * 2 + g) * QB + r) * hidden +
+                                 it.h * HD + half * 32;
+#pragma unroll
+            for (int j = 0; j < 4; j += 2) {
+              uint4 w[2];
+#pragma unroll
+              for (int u = 0; u < 2; ++u) {
+                const int c = (j + u) * 8;
+                w[u].x = pack_bf16x2(__uint_as_float(v[c + 0]) * inv, __uint_as_float(v[c + 1]) * inv);
+                w[u].y = pack_bf16x2(__uint_as_float(v[c + 2]) * inv, __uint_as_float(v[c + 3]) * inv);
+                w[u].z = pack_bf16x2(__uint_as_float(v[c + 4]) * inv, __uint_as_float(v[c + 5]) * inv);
+                w[u].w = pack_bf16x2(__uint_as_float(v[c + 6]) * inv, __uint_as_float(v[c + 7]) * inv);
+              }
+              st_global_256(dst + j * 8, w[0], w[1]);
+            }
+          }
+        }
+        tc_fence_before();  // the read of O is ordered before this thread's next P_FULL arrival
+      }
+      pair_next(it, meta, my_items, heads, qpairs);
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 16) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 }  // namespace
 
 // developer hook (dev_check): device buffer of 64 x 8 u64 that CTA 0 of the S=128 kernel fills
@@ -684,6 +1010,8 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
                                     ATT_SMEM));
     B2_CUDA_OK(cudaFuncSetAttribute(attention_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     ATT_SMEM));
+    B2_CUDA_OK(cudaFuncSetAttribute(attention_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    PAIR_SMEM));
     configured[dev] = true;
   }
   const int heads = hidden / HD, qblocks = S / QB;
@@ -699,15 +1027,28 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
     const char* e = getenv("B2_ATT_CTAS_PER_SM");
     return e && atoi(e) == 1 ? 1 : 2;
   }();
+  static const bool use_stream = [] {  // developer knob: B2_ATT_STREAM=1 keeps the first S > 128 kernel (A/B runs)
+    const char* e = getenv("B2_ATT_STREAM");
+    return e && atoi(e) == 1;
+  }();
   int ctas = items < per_sm * sms ? static_cast<int>(items) : per_sm * sms;
   if (S == QB) {
     const int need = static_cast<int>((items + PERSIST_MAX_ITEMS - 1) / PERSIST_MAX_ITEMS);
     if (ctas < need) ctas = need;  // a CTA's item list must fit its shared-memory table
     attention_persist_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(maps, out, lens, S, hidden, heads,
                                                                       static_cast<int>(items), cu, g_att_trace);
-  } else {
+  } else if (use_stream) {
     attention_stream_kernel<<<ctas, ATT_THREADS, ATT_SMEM, stream>>>(maps, out, lens, S, hidden, heads, qblocks,
                                                                      static_cast<int>(items), cu);
+  } else {
+    // one CTA per SM, work item = (sequence, head, pair of query blocks)
+    const int qpairs = (qblocks + 1) / 2;
+    const long long pitems = 1ll * B * heads * qpairs;
+    int grid = pitems < sms ? static_cast<int>(pitems) : sms;
+    const int need = static_cast<int>((pitems + PAIR_MAX_ITEMS - 1) / PAIR_MAX_ITEMS);
+    if (grid < need) grid = need;  // a CTA's item list must fit its shared-memory table
+    attention_pair_kernel<<<grid, PAIR_THREADS, PAIR_SMEM, stream>>>(maps, out, lens, S, hidden, heads, qpairs,
+                                                                     static_cast<int>(pitems), cu);
   }
   B2_CUDA_OK(cudaGetLastError());
   return B2_OK;

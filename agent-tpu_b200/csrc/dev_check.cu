@@ -109,11 +109,20 @@ static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it, b
   return bad ? 1 : 0;
 }
 
-static int check_attention(int B, int S, int hidden, const std::vector<int>& lens_in, bool time_it) {
+// late_k_gain > 1 multiplies the K rows of every key block after the first by it: each later block's
+// scores then tower over the running maximum, which is what makes a lazy-rescale kernel rescale.
+static int check_attention(int B, int S, int hidden, const std::vector<int>& lens_in, bool time_it,
+                           float late_k_gain = 1.0f) {
   const int rows = B * S, heads = hidden / 64;
   std::vector<float> f((size_t)rows * 3 * hidden);
   std::vector<__nv_bfloat16> hq(f.size());
-  for (size_t i = 0; i < f.size(); ++i) { f[i] = bf16_round(frand() * 2.0f); hq[i] = __float2bfloat16(f[i]); }
+  for (size_t i = 0; i < f.size(); ++i) {
+    float v = frand() * 2.0f;
+    const size_t row = i / (3 * (size_t)hidden), col = i % (3 * (size_t)hidden);
+    if (late_k_gain != 1.0f && col >= (size_t)hidden && col < 2 * (size_t)hidden)
+      v *= powf(late_k_gain, (float)((row % S) / 128));
+    f[i] = bf16_round(v); hq[i] = __float2bfloat16(f[i]);
+  }
   std::vector<int32_t> lens(B);
   for (int b = 0; b < B; ++b) lens[b] = lens_in[b % lens_in.size()];
   __nv_bfloat16 *dq, *dout;
@@ -165,7 +174,10 @@ static int check_attention(int B, int S, int hidden, const std::vector<int>& len
     CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
     float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= 10;
     double bytes = (double)rows * hidden * 2 * 4;
-    printf("  time %.3f ms  %.1f GB/s (Q,K,V,O once)\n", ms, bytes / ms / 1e6);
+    double flop = 0;
+    for (int b = 0; b < B; ++b) flop += 4.0 * (double)lens[b] * lens[b] * hidden;
+    printf("  time %.3f ms  %.1f GB/s (Q,K,V,O once)  %.1f TFLOP/s (4*len^2*H per sequence)\n", ms, bytes / ms / 1e6,
+           flop / ms / 1e9);
   }
   cudaFree(dq); cudaFree(dout); cudaFree(dl);
   return bad ? 1 : 0;
@@ -334,6 +346,20 @@ int main(int argc, char** argv) {
     fails += check_attention(3, 128, 128, {128, 37, 2}, false);
     fails += check_attention(5, 512, 128, {512, 300, 129, 5, 128}, false);
     fails += check_attention(64, 128, 768, {128, 16, 77, 100}, false);
+  }
+  if (!strcmp(what, "all") || !strcmp(what, "attn") || !strcmp(what, "attnlong")) {
+    // S > 128: every tile edge, one- and two-block query pairs, solo second blocks, rescaling data
+    fails += check_attention(14, 512, 128, {512, 511, 510, 385, 384, 383, 257, 256, 255, 129, 128, 127, 2, 1}, false);
+    fails += check_attention(9, 256, 128, {256, 255, 129, 128, 127, 65, 64, 33, 1}, false);
+    fails += check_attention(7, 384, 128, {384, 383, 300, 257, 256, 200, 100}, false);
+    fails += check_attention(12, 512, 128, {512, 500, 400, 385, 300, 260}, false, 3.0f);   // forces O rescales
+    fails += check_attention(40, 512, 768, {512, 300, 447, 258, 129, 384}, false);
+    fails += check_attention(300, 512, 768, {256, 300, 350, 400, 450, 510, 275, 333}, false);   // many items per CTA
+  }
+  if (!strcmp(what, "attnperf512")) {
+    fails += check_attention(256, 512, 768, {512}, true);
+    fails += check_attention(256, 512, 768, {512, 300}, true);
+    fails += check_attention(1024, 512, 768, {256, 300, 350, 400, 450, 510, 275, 333}, true);
   }
   if (!strcmp(what, "all") || !strcmp(what, "attnperf")) {
     fails += check_attention(1024, 128, 768, {128}, true);
