@@ -109,6 +109,94 @@ static int check_gemm(int M, int N, int K, int epi, int num_sms, bool time_it, b
   return bad ? 1 : 0;
 }
 
+// The production epilogue of the out-projection and FFN2: C = A·Wᵀ + b + LayerNorm(U)·γ + β rebuilt from
+// the un-normalised residual rows U and their partial sums, with the (Σ, Σ²) of C written per 64 columns.
+static int check_gemm_lnres(int M, int N, int K, int num_sms, bool time_it, bool finished_stats = false) {
+  const int slots = (N + 63) / 64;
+  std::vector<__nv_bfloat16> hA((size_t)M * K), hW((size_t)N * K), hU((size_t)M * N);
+  std::vector<float> fA(hA.size()), fW(hW.size()), fU(hU.size()), hb(N), hg(N), hbe(N);
+  for (size_t i = 0; i < hA.size(); ++i) { fA[i] = bf16_round(frand()); hA[i] = __float2bfloat16(fA[i]); }
+  for (size_t i = 0; i < hW.size(); ++i) { fW[i] = bf16_round(frand() * 0.05f); hW[i] = __float2bfloat16(fW[i]); }
+  for (size_t i = 0; i < hU.size(); ++i) { fU[i] = bf16_round(frand() * 2.0f + 0.5f); hU[i] = __float2bfloat16(fU[i]); }
+  for (int i = 0; i < N; ++i) { hb[i] = frand() * 0.5f; hg[i] = 1.0f + 0.5f * frand(); hbe[i] = frand(); }
+  std::vector<float2> hpart((size_t)M * slots), hstats(M);
+  for (int m = 0; m < M; ++m) {
+    double s = 0, q = 0;
+    for (int sl = 0; sl < slots; ++sl) {
+      float ps = 0, pq = 0;
+      for (int c = sl * 64; c < std::min(N, sl * 64 + 64); ++c) { float u = fU[(size_t)m * N + c]; ps += u; pq += u * u; }
+      hpart[(size_t)m * slots + sl] = make_float2(ps, pq);
+      s += ps; q += pq;
+    }
+    const double mean = s / N, var = std::max(q / N - mean * mean, 0.0);
+    hstats[m] = make_float2((float)mean, (float)(1.0 / sqrt(var + 1e-12)));
+  }
+  __nv_bfloat16 *dA, *dW, *dC, *dU;
+  float *db, *dg, *dbe;
+  float2 *dpart, *dpout, *dstats;
+  CK(cudaMalloc(&dA, hA.size() * 2)); CK(cudaMalloc(&dW, hW.size() * 2));
+  CK(cudaMalloc(&dC, hU.size() * 2)); CK(cudaMalloc(&dU, hU.size() * 2));
+  CK(cudaMalloc(&db, N * 4)); CK(cudaMalloc(&dg, N * 4)); CK(cudaMalloc(&dbe, N * 4));
+  CK(cudaMalloc(&dpart, hpart.size() * 8)); CK(cudaMalloc(&dpout, hpart.size() * 8)); CK(cudaMalloc(&dstats, M * 8));
+  CK(cudaMemcpy(dA, hA.data(), hA.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dW, hW.data(), hW.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dU, hU.data(), hU.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(db, hb.data(), N * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dg, hg.data(), N * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dbe, hbe.data(), N * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dpart, hpart.data(), hpart.size() * 8, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dstats, hstats.data(), M * 8, cudaMemcpyHostToDevice));
+  CK(cudaMemset(dC, 0xFF, hU.size() * 2));
+  CUtensorMap ta, tb, tc, tr;
+  B2(gemm_tmap_a(&ta, dA, M, K, K));
+  B2(gemm2_tmap_b(&tb, dW, N, K));
+  B2(gemm2_tmap_c(&tc, dC, M, N, N));
+  B2(gemm2_tmap_c(&tr, dU, M, N, N));
+  GemmLnArgs a;
+  if (finished_stats) a.row_stats = dstats; else a.part_in = dpart;
+  a.inv_h = 1.0f / N; a.eps = 1e-12f; a.res_gamma = dg; a.res_beta = dbe; a.part_out = dpout; a.part_slots = slots;
+  auto run = [&]() { return gemm2_bf16_tn(0, ta, tb, tc, &tr, db, M, N, K, GEMM_EPI_LNRES_STATS, num_sms, nullptr, &a); };
+  B2(run());
+  CK(cudaDeviceSynchronize());
+  std::vector<__nv_bfloat16> hC(hU.size());
+  std::vector<float2> hpo(hpart.size());
+  CK(cudaMemcpy(hC.data(), dC, hC.size() * 2, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(hpo.data(), dpout, hpo.size() * 8, cudaMemcpyDeviceToHost));
+  double max_err = 0; size_t bad = 0, checked = 0;
+  const size_t total = (size_t)M * N, step = total > (1u << 20) ? total / (1u << 17) + 1 : 1;
+  for (size_t idx = 0; idx < total; idx += step) {
+    const int m = idx / N, n = idx % N;
+    double acc = 0;
+    for (int k = 0; k < K; ++k) acc += (double)fA[(size_t)m * K + k] * fW[(size_t)n * K + k];
+    acc += hb[n] + ((double)fU[idx] - hstats[m].x) * hstats[m].y * hg[n] + hbe[n];
+    const double got = __bfloat162float(hC[idx]), err = fabs(got - acc);
+    if (!(err <= 0.01 * fabs(acc) + 0.02)) { if (bad < 5) printf("  mismatch m=%d n=%d got=%f want=%f\n", m, n, got, acc); ++bad; }
+    max_err = std::max(max_err, err); ++checked;
+  }
+  // the emitted partial sums against the stored (rounded) output rows, a few rows
+  for (int m = 0; m < M; m += std::max(1, M / 64)) for (int sl = 0; sl < slots; ++sl) {
+    double ps = 0;
+    for (int c = sl * 64; c < std::min(N, sl * 64 + 64); ++c) ps += __bfloat162float(hC[(size_t)m * N + c]);
+    if (fabs(ps - hpo[(size_t)m * slots + sl].x) > 0.5) { if (bad < 5) printf("  part_out mismatch m=%d slot=%d\n", m, sl); ++bad; }
+  }
+  printf("gemm2 LNRES_STATS M=%d N=%d K=%d (%s): checked=%zu bad=%zu max_abs_err=%.5f %s\n", M, N, K,
+         finished_stats ? "finished stats" : "partial sums in", checked, bad, max_err, bad ? "FAIL" : "ok");
+  if (time_it && !bad) {
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (int i = 0; i < 10; ++i) B2(run());
+    for (int rep = 0; rep < 3; ++rep) {   // three blocks of 50: the spread between them is the noise floor
+      CK(cudaEventRecord(e0));
+      for (int i = 0; i < 50; ++i) B2(run());
+      CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+      float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= 50;
+      printf("  time %.4f ms  %.1f TFLOP/s\n", ms, 2.0 * M * N * K / ms / 1e9);
+    }
+  }
+  cudaFree(dA); cudaFree(dW); cudaFree(dC); cudaFree(dU); cudaFree(db); cudaFree(dg); cudaFree(dbe);
+  cudaFree(dpart); cudaFree(dpout); cudaFree(dstats);
+  return bad ? 1 : 0;
+}
+
 // late_k_gain > 1 multiplies the K rows of every key block after the first by it: each later block's
 // scores then tower over the running maximum, which is what makes a lazy-rescale kernel rescale.
 static int check_attention(int B, int S, int hidden, const std::vector<int>& lens_in, bool time_it,
@@ -365,6 +453,29 @@ int main(int argc, char** argv) {
     fails += check_attention(1024, 128, 768, {128}, true);
     fails += check_attention(1024, 128, 768, {16, 40, 72, 100, 126}, true);
     fails += check_attention(256, 512, 768, {512, 300}, true);
+  }
+  if (!strcmp(what, "lnres")) {   // the production out-projection / FFN2 epilogue: correctness, time, timeline
+    fails += check_gemm_lnres(1000, 768, 768, sms, false);
+    fails += check_gemm_lnres(71000, 768, 768, sms, true);
+    fails += check_gemm_lnres(71000, 768, 768, sms, true, true);
+    fails += check_gemm_lnres(71000, 768, 3072, sms, true);
+    fails += check_gemm(71000, 768, 768, GEMM_EPI_BIAS_RESIDUAL, sms, true, true);
+    fails += check_gemm(71000, 2304, 768, GEMM_EPI_BIAS, sms, true, true);
+    unsigned long long* dtr; CK(cudaMalloc(&dtr, 2 * 32 * 8 * 8));
+    CK(cudaMemset(dtr, 0, 2 * 32 * 8 * 8));
+    gemm2_set_trace(dtr, 0);
+    check_gemm_lnres(71000, 768, 768, sms, false);
+    gemm2_set_trace(nullptr, 0);
+    std::vector<unsigned long long> tr(2 * 32 * 8);
+    CK(cudaMemcpy(tr.data(), dtr, tr.size() * 8, cudaMemcpyDeviceToHost));
+    const unsigned long long t0 = tr[0];
+    printf("LNRES_STATS N=768 K=768  tile: mma[stage free, issued] epi[staging free, acc ready, residual, half 1, "
+           "half 2, stored]  (ns); SM clock %.0f MHz\n", 1e3 * double(tr[256 + 11 * 8] - tr[256]) / double(tr[11 * 8] - tr[0]));
+    for (int i = 0; i < 12; ++i) {
+      printf("%2d:", i);
+      for (int k = 0; k < 8; ++k) printf(" %7lld", tr[i * 8 + k] ? (long long)(tr[i * 8 + k] - t0) : -1ll);
+      printf("\n");
+    }
   }
   if (!strcmp(what, "gemm2trace")) {
     unsigned long long* dtr; CK(cudaMalloc(&dtr, 2 * 32 * 8 * 8));
