@@ -849,7 +849,7 @@ def run_csv(args, wl_name: str, wl: dict, D: Dist):
     index_gbs = size / float(info.index_ms) / 1e6
     traffic, traffic_src = load_traffic("csv_classify_kernel")
     cpu = None
-    if world == 1 or args.single_process:
+    if world == 1 and n_dev == 1:    # the CPU legs run on the one-GPU line only (box time on N GPUs is charged N times)
         rate, done, dt = cpu_csv_rate(path, rows, 2_000_000)
         crate, cdone, cdt, cores = cpu_classify_rate(model, vocab, sentence_pool(wl, 4096), S, budget_s=10.0, max_items=1024)
         chain_cpu = 1.0 / (1.0 / rate + 1.0 / crate)
