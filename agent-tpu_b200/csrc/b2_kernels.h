@@ -70,6 +70,12 @@ int attention_bf16(cudaStream_t stream, const AttentionMaps& tqkv, __nv_bfloat16
 void attention_set_trace(unsigned long long* dev_buf);  // developer timeline hook (dev_check)
 void gemm2_set_trace(unsigned long long* dev_buf, int debug_mode = 0);  // same for the pair GEMM
 
+// developer micro-benchmark (b2_pace.cu, dev_check tmapace): the pair GEMM's operand stream alone,
+// unicast (mode 0) or with the W tile multicast across a cluster of two CTA pairs (mode 1)
+// `stages` = ring depth (3..7, mode 0); hold > 0: the consumer keeps each slot that many cycles, in order
+int tma_pace(cudaStream_t stream, int mode, int stages, int hold, const void* A, int rows, const void* W, int n,
+             int K, int tiles, int num_sms, unsigned long long* cycles, int* grid_out);
+
 // developer aid: bounded waits that give up record where (b2_common.cuh: mbar_wait_timeout)
 int gemm_set_trap_log(unsigned long long* mapped);
 int gemm2_set_trap_log(unsigned long long* mapped);

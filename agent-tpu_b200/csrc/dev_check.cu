@@ -477,6 +477,35 @@ int main(int argc, char** argv) {
       printf("\n");
     }
   }
+  if (!strcmp(what, "tmapace")) {
+    // the pair GEMM's operand stream alone (no MMAs): cycles per 64-deep K step.
+    //  (1) unicast vs W multicast over two pairs, slots released at once;
+    //  (2) ring depth 3..7 with every slot held 512 cycles in order, as the tensor pipe holds it
+    const int rows = 71000 / 256 * 256, K = 768, n = 2304;
+    __nv_bfloat16 *dA, *dW;
+    unsigned long long* dc;
+    CK(cudaMalloc(&dA, (size_t)rows * K * 2)); CK(cudaMalloc(&dW, (size_t)n * K * 2)); CK(cudaMalloc(&dc, 2 * 160 * 8));
+    CK(cudaMemset(dA, 0, (size_t)rows * K * 2)); CK(cudaMemset(dW, 0, (size_t)n * K * 2));
+    const int tiles = 60, steps = tiles * (K / 64);
+    auto run = [&](int mode, int stages, int hold) {
+      double best = 1e30;
+      for (int rep = 0; rep < 4; ++rep) {
+        int grid = 0;
+        if (tma_pace(0, mode, stages, hold, dA, rows, dW, n, K, tiles, sms, dc, &grid)) { printf("tma_pace failed: %s\n", b2::last_error()); return; }
+        CK(cudaDeviceSynchronize());
+        std::vector<unsigned long long> c(2 * grid);
+        CK(cudaMemcpy(c.data(), dc, c.size() * 8, cudaMemcpyDeviceToHost));
+        double cons = 0;
+        for (int i = 0; i < grid; ++i) cons += c[2 * i + 1];
+        if (rep) best = std::min(best, cons / grid / steps);
+      }
+      printf("tmapace mode %d (%s) stages %d hold %3d: %.1f cycles per K step\n", mode,
+             mode ? "W quarters multicast over 2 pairs" : "unicast", stages, hold, best);
+    };
+    run(0, 5, 0); run(1, 5, 0);
+    for (int hold : {512, 400}) for (int st = 3; st <= 7; ++st) run(0, st, hold);
+    cudaFree(dA); cudaFree(dW); cudaFree(dc);
+  }
   if (!strcmp(what, "gemm2trace")) {
     unsigned long long* dtr; CK(cudaMalloc(&dtr, 2 * 32 * 8 * 8));
     const int shapes[4][3] = {{2304, 768, GEMM_EPI_BIAS}, {768, 768, GEMM_EPI_BIAS_RESIDUAL},
