@@ -283,10 +283,21 @@ def run_reference(args, wl_name: str, wl: dict, rank: int, world: int):
     total = args.steps + args.warmup
     torch, bo = _oracle()
     cores = torch.get_num_threads()
+    extra = None
     if wl["kind"] == "classify":
         per_step = 64 if S == 128 else 16
         texts = make_inputs(wl, per_step * total, 1, 0)[0]
         cfg, W = bo.load_model(model)
+        # the same `config` as our arm, key for key: its inputs are a pure function of (workload, items,
+        # steps, warmup), so their mean token count is computed here with the oracle tokenizer
+        tok = 0
+        for t in make_inputs(wl, n, total, 0)[args.warmup:]:
+            tok += int(bo.tokenize(vocab, t, S)[1].sum())
+        world_cfg = max(1, args.gpus)
+        extra = {"collective": "one NCCL all-reduce of int64[16+8] per step" if world_cfg > 1 else "none (1 GPU)",
+                 "tokens_per_item_mean": round(tok / (n * args.steps), 1),
+                 "token_rows": "packed: pad positions are never materialised (results bit-identical to the padded "
+                               "layout); kernel rooflines count real token rows"}
 
         def step(i):
             chunk = texts[i * per_step:(i + 1) * per_step]
@@ -326,7 +337,7 @@ def run_reference(args, wl_name: str, wl: dict, rank: int, world: int):
         "impl": "reference", "metric": wl["metric"], "value": value, "unit": wl["unit"], "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(wl_name, wl, n, max(1, args.gpus)),
+        "config": workload_config(wl_name, wl, n, max(1, args.gpus), extra),
         "cpu_baseline": {"value": value, "unit": wl["unit"], "cores": cores, "kind": "port",
                          "sample": f"{what}; {args.steps} timed steps after {args.warmup} warm-up steps",
                          "reference_stub": REFERENCE_STUB},
