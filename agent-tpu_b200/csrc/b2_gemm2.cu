@@ -254,6 +254,10 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const uint32_t buf = sOut + quarter * OUT_BYTES;
     uint8_t* buf_ptr = smem_raw + (buf - raw) + r_local * 128;
     const uint32_t sw = static_cast<uint32_t>(r_local & 7);
+    // Phase of this quarter's residual barrier. It flips with every tile in which the quarter loads a
+    // residual block — not with every tile: when N is not a multiple of 256 (hidden 384, 640, 896) the
+    // quarters beyond N sit out the last column tile of each row block.
+    uint32_t rphase = 0;
     int it = 0;
     for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
       const int m_blk = t / n_tiles, n_blk = t % n_tiles;
@@ -302,7 +306,10 @@ gemm2_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_wait(tfull_bar(as), aphase);
       if (warp == 0 && lane == 0) stamp(it, 3);
       tc_fence_after();
-      if (kResidual && active) mbar_wait(rfull_bar(quarter), it & 1);
+      if (kResidual && active) {
+        mbar_wait(rfull_bar(quarter), rphase);
+        rphase ^= 1u;
+      }
       if (warp == 0 && lane == 0) stamp(it, 4);
       const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + quarter * 64;
 #pragma unroll

@@ -456,6 +456,9 @@ int main(int argc, char** argv) {
   }
   if (!strcmp(what, "lnres")) {   // the production out-projection / FFN2 epilogue: correctness, time, timeline
     fails += check_gemm_lnres(1000, 768, 768, sms, false);
+    fails += check_gemm_lnres(3000, 384, 384, sms, false);   // N not a multiple of 256: quarters sit out column tiles
+    fails += check_gemm_lnres(3000, 640, 640, sms, false);
+    fails += check_gemm(3000, 384, 384, GEMM_EPI_BIAS_RESIDUAL, sms, false, true);
     fails += check_gemm_lnres(71000, 768, 768, sms, true);
     fails += check_gemm_lnres(71000, 768, 768, sms, true, true);
     fails += check_gemm_lnres(71000, 768, 3072, sms, true);

@@ -103,6 +103,33 @@ def test_explicit_tensor_model_file_equals_synthetic(tiny_model, vocab_path, wor
         a.close(); b.close()
 
 
+def test_hidden_size_that_is_not_a_multiple_of_256(vocab_path, work_dir, sentences):
+    """hidden 384 (6 heads), FFN 1152: the GEMMs' last 256-wide column tile is half empty, so some
+    epilogue quarters sit out every other tile — their residual barrier must keep its own phase (it
+    used to follow the tile counter). Logits and every layer against the fp32 oracle."""
+    import bert_oracle as bo
+    import model_file as mf
+    from ops import _cuda_runtime as rt
+    cfg = mf.ModelConfig(hidden=384, layers=3, heads=6, intermediate=1152, num_labels=7, init_std=0.05,
+                         classifier_std=0.1, seed=99)
+    path = mf.write_model_file(os.path.join(work_dir, "h384.b2m"), cfg)
+    texts = sentences[:48]
+    c, W = bo.load_model(path)
+    ids, mask = bo.tokenize(vocab_path, texts, 128)
+    ref, ref_hidden = bo.forward(c, W, ids, mask, return_hidden=True)
+    eng = rt.Engine(path, vocab_path, max_batch=48, max_len=128)
+    try:
+        out = eng.classify(texts, 128, 3, want_logits=True)
+        hidden, _ = eng.debug_hidden_states(ids, mask)
+    finally:
+        eng.close()
+    assert np.abs(out["logits"] - ref).max() <= LOGIT_TOL
+    live = mask.astype(bool)
+    for l in range(cfg.layers):
+        rel = np.abs(hidden[l][live] - ref_hidden[l][live]).max() / np.abs(ref_hidden[l][live]).max()
+        assert rel <= 0.02, (l, rel)
+
+
 def test_batch_size_and_order_independence(tiny_model, vocab_path, sentences):
     from ops import _cuda_runtime as rt
     texts = sentences[:150] + [""] + sentences[150:200]
