@@ -236,6 +236,38 @@ def test_trained_like_layernorm_statistics_folded_and_explicit(vocab_path, work_
     assert np.abs(lp - ref_logits).max() <= max(2e-2, 2e-2 * span)
 
 
+def test_bart_encoder_on_these_kernels(work_dir):
+    """SURVEY.md section 8(f) row 4, the part that can be checked offline: the ENCODER of the reference's
+    `map_summarize` model (BART-base geometry: 6 layers x 768, 12 heads, FFN 3072, erf-GELU, post-LN;
+    ops/map_summarize.py:29-30) runs on this library's kernels unchanged. A random-init transformers
+    BartEncoder is written as a .b2m file (tests/bart_encoder.py: q/k/v stacked, positions offset by 2,
+    zero token types) and every layer's output is compared with BartEncoder's own hidden states — the
+    third party itself, not this repo's oracle. The decoder and beam search of the op are not built."""
+    import bart_encoder as be
+    from ops import _cuda_runtime as rt
+    model = be.random_bart(layers=6)
+    path, cfg = be.encoder_as_model_file(model, os.path.join(work_dir, "bart_encoder.b2m"))
+    for S, lengths in ((128, [1, 2, 31, 64, 97, 127, 128] + list(np.random.default_rng(9).integers(4, 129, 57))),
+                       (512, [129, 255, 256, 257, 384, 385, 510, 512])):
+        ids, mask = _rows(lengths, S, cfg.vocab_size, seed=31)
+        ref = be.bart_hidden_states(model, ids, mask)
+        eng = rt.Engine(path, None, max_batch=len(lengths), max_len=S)
+        try:
+            got, _ = eng.debug_hidden_states(ids, mask)
+        finally:
+            eng.close()
+        worst = 0.0
+        for l in range(cfg.layers + 1):
+            mk = mask.copy()
+            if l == cfg.layers:
+                mk[:, 1:] = 0                       # the last layer is computed for position 0 only
+            g_inf, g_row, g_cos = _layer_errors(ref[l], got[l], mk)
+            worst = max(worst, g_inf)
+            assert g_inf <= 0.03 and g_row <= 0.02 and g_cos >= COS_MIN, (S, l, g_inf, g_row, g_cos)
+        print(f"\n[BART-base encoder, S={S}] worst per-layer rel-inf error vs transformers BartEncoder: {worst:.5f}")
+    os.remove(path)
+
+
 def test_masks_that_are_not_prefixes_are_refused(tiny_model, vocab_path, clean_env):
     """b2_classify_ids stores sequence b as rows [0, len_b): a mask with a hole, left padding or no
     token would silently be classified as another input, so it is refused (B2_ERR_ARG) and the op

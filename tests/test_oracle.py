@@ -88,3 +88,26 @@ def test_chunk_oracle_reproduces_the_reference_map_tokenize(ref_golden):
     for case in ref_golden["map_tokenize"]:
         assert chunk_oracle.map_tokenize(case["payload"]) == case["result"], case["payload"]
     assert chunk_oracle.map_tokenize(None) == {"ok": True, "tokens": [], "count": 0, "total_chars": 0}
+
+
+def test_bart_encoder_maps_onto_the_model_file(tmp_path):
+    """The encoder of `map_summarize`'s model (BART: ops/map_summarize.py:29-30) is this library's layer
+    with different embeddings: a random-init transformers BartEncoder written as a .b2m file
+    (tests/bart_encoder.py) and run through the fp32 oracle reproduces BartEncoder's own hidden
+    states. The GPU counterpart is tests/test_gpu_parity_layers.py::test_bart_encoder_on_these_kernels."""
+    import bart_encoder as be
+    import bert_oracle as bo
+    model = be.random_bart(layers=2)
+    path, cfg = be.encoder_as_model_file(model, str(tmp_path / "bart_enc.b2m"))
+    rng = np.random.default_rng(0)
+    lens, S = [1, 5, 64, 128], 128
+    ids = np.ones((len(lens), S), np.int32)
+    mask = np.zeros((len(lens), S), np.uint8)
+    for i, L in enumerate(lens):
+        ids[i, :L] = rng.integers(3, cfg.vocab_size, L)
+        mask[i, :L] = 1
+    c, W = bo.load_model(path)
+    _, hs = bo.forward(c, W, ids, mask, return_hidden=True)
+    ref = be.bart_hidden_states(model, ids, mask)
+    assert hs.shape == ref.shape == (3, 4, S, 768)
+    assert np.abs(hs - ref).max() < 2e-5
