@@ -11,6 +11,9 @@ Workloads (BASELINE.json `configs`; the default is the one the headline metric i
   classify512       config 4: long documents of 256-510 pieces, S = 512, batch 1,024
   tokenize          config 2: WordPiece tokenize-and-pad of synthetic lines (lines/s)
   csv_chain         config 5: csv_shard -> map_tokenize -> map_classify over a synthetic CSV (rows/s)
+  agent_loop        config 1: 1,024 sentences as leased tasks of 32 through the agent's job loop and a local
+                    controller (HTTP lease / result protocol of app.py); `--impl reference` drives the CPU port
+                    through the same loop
 
 A step is one pass of the hot path over `--items` units per GPU. One process per GPU under torchrun;
 units shard as contiguous slices with no data-path collective; the per-job label histogram and
@@ -59,6 +62,9 @@ WORKLOADS = {
     "csv_chain": dict(kind="csv", S=128, items=262_144, min_tok=16, max_tok=126,
                       metric="csv_shard -> map_tokenize -> map_classify rows/sec (seq 128)", unit="rows/s",
                       config="BASELINE config 5 shape"),
+    "agent_loop": dict(kind="loop", S=128, items=1024, min_tok=16, max_tok=126,
+                       metric="map_classify_tpu items/sec through the agent job loop (batch 32)", unit="items/s",
+                       config="BASELINE config 1 shape: leased tasks of 32 sentences through the lease / result protocol"),
 }
 # B1: the literal reference op, ops.get_op("map_classify_tpu")(payload) imported from
 # /root/reference, measured in the build container — the checkout does not exist on the GPU box.
@@ -896,6 +902,98 @@ def run_csv(args, wl_name: str, wl: dict, D: Dist):
     eng.close()
 
 
+# ------------------------------------------------------------------------------------------------
+# agent loop workload (config 1)
+# ------------------------------------------------------------------------------------------------
+def run_agent_loop(args, wl_name: str, wl: dict, rank: int, reference: bool):
+    """A local controller hands out one warm-up task and then `items / 32` tasks of 32 sentences; an agent
+    process leases them one at a time, calls `tpu_ops.map_classify_tpu(payload)` and posts the results
+    (the protocol of the reference's app.py:161-234, spoken here by tests/tools/agent_loop_standin.py —
+    the reference checkout does not exist on the GPU box). Timed on the controller's clock from the
+    warm-up task's result to the last result. With --impl reference the agent's `tpu_ops` is the CPU
+    port (oracle/loop_shim), so both arms pay the same protocol costs."""
+    if rank != 0:
+        return
+    import threading
+    from http.server import BaseHTTPRequestHandler, HTTPServer
+    model, vocab, _ = prepare_files("loop")
+    n = args.items or wl["items"]
+    per_task = 32
+    texts = make_inputs(wl, n, 1, 0)[0]
+    tasks = [texts[:per_task]] + [texts[i:i + per_task] for i in range(0, n, per_task)]   # [0] = warm-up
+    st = {"next": 0, "results": [], "t_first": None, "t_last": None}
+
+    class H(BaseHTTPRequestHandler):
+        def log_message(self, *a):
+            pass
+
+        def do_POST(self):
+            body = json.loads(self.rfile.read(int(self.headers["Content-Length"])))
+            if self.path == "/v1/leases":
+                if st["next"] >= len(tasks):
+                    self.send_response(204); self.end_headers(); return
+                i = st["next"]; st["next"] += 1
+                out = {"lease_id": f"L{i}", "tasks": [{"id": f"job-{i}", "op": "map_classify_tpu", "job_epoch": 1,
+                                                       "payload": {"items": tasks[i], "topk": TOPK, "batch": per_task}}]}
+            else:
+                now = time.perf_counter()
+                if body.get("job_id") == "job-0":
+                    st["t_first"] = now
+                st["t_last"] = now
+                st["results"].append(body)
+                out = {"ok": True}
+            raw = json.dumps(out).encode()
+            self.send_response(200); self.send_header("Content-Type", "application/json")
+            self.send_header("Content-Length", str(len(raw))); self.end_headers(); self.wfile.write(raw)
+
+    srv = HTTPServer(("127.0.0.1", 0), H)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    shim = os.path.join(ROOT, "oracle", "loop_shim") if reference else os.path.join(ROOT, "agent-tpu_b200")
+    env = dict(os.environ, CONTROLLER_URL=f"http://127.0.0.1:{srv.server_port}", PYTHONPATH=shim,
+               CUDA_MODEL_PATH=model, CUDA_VOCAB_PATH=vocab, B2_DEVICE="0", AGENT_NAME="bench-agent")
+    agent = os.path.join(ROOT, "tests", "tools", "agent_loop_standin.py")
+    sampler = None if reference else ClockSampler(0)
+    p = subprocess.run([sys.executable, agent, "900"], env=env, capture_output=True, text=True, timeout=1200)
+    clocks = sampler.stop() if sampler else None
+    srv.shutdown()
+    done = [r for r in st["results"] if r.get("job_id") != "job-0"]
+    bad = [r for r in st["results"] if r.get("status") != "succeeded" or "fallback" in (r.get("result") or {})]
+    if len(done) != len(tasks) - 1 or bad:
+        raise RuntimeError(f"agent loop: {len(done)} of {len(tasks) - 1} results, {len(bad)} failed: "
+                           f"{(bad or [None])[0]} {p.stdout[-500:]} {p.stderr[-500:]}")
+    wall = st["t_last"] - st["t_first"]
+    value = n / wall
+    hist = np.sum([r["result"]["label_histogram"] for r in done], axis=0)
+    assert int(hist.sum()) == n
+    line = {
+        "metric": wl["metric"], "value": round(value, 1), "unit": wl["unit"], "n_gpus": 0 if reference else 1,
+        "steps": len(done), "warmup": 1, "ms_per_step": round(wall / len(done) * 1e3, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32" if reference else "bf16", "data": "synthetic",
+        "config": workload_config(wl_name, wl, n, 1, {"batch": per_task, "tasks": len(done), "items_per_task": per_task,
+                                                      "agent": "tests/tools/agent_loop_standin.py (the reference's "
+                                                               "lease / result protocol; its app.py is absent on the GPU box)"}),
+        "e2e": {"value": round(value, 1), "unit": wl["unit"],
+                "h2d_bytes_per_step": 0 if reference else int(sum(len(t.encode()) for t in tasks[1]) + 8 * (per_task + 1)),
+                "d2h_bytes_per_step": 0 if reference else per_task * (TOPK * 8 + 4) + C * 8,
+                "api": "controller -> HTTP lease -> agent loop -> tpu_ops.map_classify_tpu(payload) -> HTTP result; a "
+                       "step is one leased task; `value` is this same end-to-end figure (there is no device-resident form)"},
+        "gpu_launches": 0 if reference else int(sum(r["result"]["metrics"]["kernel_launches"] for r in done)),
+        "roofline": None if reference else {
+            "kernel": "gemm2_bf16_tn_kernel", "bound": "tensor", "achieved": None, "peak": load_peaks()["bf16_sustained"],
+            "unit": "TFLOP/s", "frac": None, "traffic": None,
+            "device_ms_per_task": round(float(np.mean([r["result"]["metrics"]["gpu_ms_total"] for r in done])), 3),
+            "note": "32-item tasks are launch- and protocol-bound: the kernels' share of a task is device_ms_per_task of "
+                    "ms_per_step; see the classify128 line for the kernels' roofline"},
+        "cpu_baseline": ({"value": round(value, 2), "unit": wl["unit"], "cores": os.cpu_count(), "kind": "port",
+                          "sample": f"all {n} sentences: tokenizers + fp32 torch BERT-base behind the same loop",
+                          "reference_stub": REFERENCE_STUB} if reference else None),
+        "clocks": clocks,
+    }
+    if reference:
+        line["impl"] = "reference"
+    emit(line)
+
+
 _REAL_STDOUT = None
 
 
@@ -935,6 +1033,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if wl["kind"] == "loop":
+        run_agent_loop(args, args.workload, wl, rank, args.impl == "reference")
+        return
     if args.impl == "reference":
         run_reference(args, args.workload, wl, rank, world)
         return
