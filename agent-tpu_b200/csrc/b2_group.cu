@@ -97,6 +97,14 @@ struct b2_group {
 
 namespace {
 
+// The caller's current device is put back when a group call returns: member 0's slice runs on the
+// calling thread and selects its own device.
+struct CallerDevice {
+  int prev = -1;
+  CallerDevice() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+  ~CallerDevice() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 struct SliceResult {
   int rc = B2_OK;
   std::string error;
@@ -374,6 +382,7 @@ int b2_group_classify_text(b2_group* g, const uint8_t* utf8, const int64_t* offs
     return B2_ERR_ARG;
   }
   std::lock_guard<std::mutex> lock(g->mu);
+  CallerDevice restore;
   const int W = static_cast<int>(g->members.size()), C = g->num_labels;
   static const uint8_t empty = 0;
   const uint8_t* text = utf8 ? utf8 : &empty;
@@ -416,6 +425,7 @@ int b2_group_csv_classify(b2_group* g, b2_csv* c, int32_t column, int64_t start_
     return B2_ERR_ARG;
   }
   std::lock_guard<std::mutex> lock(g->mu);
+  CallerDevice restore;
   const int W = static_cast<int>(g->members.size()), C = g->num_labels;
   std::vector<SliceResult> res(W);
   std::vector<int64_t> total;
@@ -463,7 +473,6 @@ int b2_group_csv_classify(b2_group* g, b2_csv* c, int32_t column, int64_t start_
   }
   classify_slice(0, lo0, cnt0);
   for (auto& t : th) t.join();
-  cudaSetDevice(g->devices[0]);
   return finish_job(g, res, total, max_ms, histogram, metrics, per_device);
 }
 
