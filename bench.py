@@ -88,14 +88,18 @@ def load_peaks():
         return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback"}
 
 
-def load_traffic(kernel: str):
+def load_traffic(kernel: str, units: float = None):
     """dram__bytes_read + write per launch from the latest committed `ncu --set full` capture of
     `kernel` (profiles/traffic.json: written by hand after a capture, with the commit it was taken
-    at). None when there is no capture on record — never a literal in this file."""
+    at). Kernels whose launch size varies are recorded per unit (line, file byte) and scaled by the
+    `units` of this run's launch. None when there is no capture on record — never a literal here."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)[kernel]
-        return float(t["bytes_per_launch"]), f"{t['capture']} (ncu --set full at {t['head']}: {t['what']})"
+        src = f"{t['capture']} (ncu --set full at {t['head']}: {t['what']})"
+        if "bytes_per_unit" in t:
+            return float(t["bytes_per_unit"]) * float(units), src + f", scaled to {units:.0f} {t['unit']}s"
+        return float(t["bytes_per_launch"]), src
     except Exception:
         return None, "no ncu capture on record for this kernel"
 
@@ -764,7 +768,7 @@ def run_tokenize(args, wl_name: str, wl: dict, D: Dist):
         return
     alg = float(blob.size + 8 * n + 5 * S * n)       # len(utf8) + 8 + 5*S bytes per line
     gbs = alg / (k_ms / args.steps) / 1e6
-    traffic, traffic_src = load_traffic("wordpiece_kernel")
+    traffic, traffic_src = load_traffic("wordpiece_kernel", n)
     cpu = None
     if world == 1:
         wp, ck, cores = cpu_tokenize_rate(vocab, texts, S, budget_s=10.0)
@@ -864,7 +868,7 @@ def run_csv(args, wl_name: str, wl: dict, D: Dist):
     e2e_value = rows / (open_ms / 1e3 + wall / args.steps)   # one job: open (copy + index) + classify
     peaks = load_peaks()
     index_gbs = size / float(info.index_ms) / 1e6
-    traffic, traffic_src = load_traffic("csv_classify_kernel")
+    traffic, traffic_src = load_traffic("csv_classify_kernel", size)
     cpu = None
     if world == 1 and n_dev == 1:    # the CPU legs run on the one-GPU line only (box time on N GPUs is charged N times)
         rate, done, dt = cpu_csv_rate(path, rows, 2_000_000)
