@@ -1020,7 +1020,6 @@ def emit(line: dict) -> None:
 
 
 def main():
-    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -1037,17 +1036,20 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "ours" and wl["kind"] != "loop" and world != args.gpus and world == 1 and args.gpus > 1 \
+            and not args.single_process:
+        # launched without torchrun: re-exec under it on one node (before stdout is claimed below — the
+        # re-executed ranks must inherit the real stdout for their JSON line)
+        os.execvp(sys.executable, [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                                   f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
+                                   "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:])
+    claim_stdout()
     if wl["kind"] == "loop":
         run_agent_loop(args, args.workload, wl, rank, args.impl == "reference")
         return
     if args.impl == "reference":
         run_reference(args, args.workload, wl, rank, world)
         return
-    if world != args.gpus and world == 1 and args.gpus > 1 and not args.single_process:
-        # launched without torchrun: re-exec under it on one node
-        os.execvp(sys.executable, [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
-                                   f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
-                                   "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:])
     D = Dist(rank, local_rank, world)
     {"classify": run_classify, "tokenize": run_tokenize, "csv": run_csv}[wl["kind"]](args, args.workload, wl, D)
     if world > 1:
