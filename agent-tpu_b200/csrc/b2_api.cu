@@ -1070,8 +1070,9 @@ int b2_tokenize_device(b2_handle* h, const uint8_t* d_utf8, const int64_t* d_off
   return B2_OK;
 }
 
+// copy_text = false: size the buffers and upload the offsets only (the caller uploads the text in pieces)
 static int stage_text(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n,
-                      int64_t* n_bytes) {
+                      int64_t* n_bytes, bool copy_text = true) {
   if (!offsets || n < 0 || n > 0x7fffffff || (n > 0 && !utf8 && offsets[n] > 0)) {
     set_last_error("text input: n out of range or NULL utf8 / offsets");
     return B2_ERR_ARG;
@@ -1084,9 +1085,72 @@ static int stage_text(b2_handle* h, const uint8_t* utf8, const int64_t* offsets,
   int rc;
   if ((rc = grow(reinterpret_cast<void**>(&h->st_text), &h->st_text_cap, bytes + 16))) return rc;
   if ((rc = grow(reinterpret_cast<void**>(&h->st_off), &h->st_off_cap, (n + 1) * 8))) return rc;
-  if (bytes) B2_CUDA_OK(cudaMemcpyAsync(h->st_text, utf8, bytes, cudaMemcpyHostToDevice, h->stream));
+  if (bytes && copy_text) B2_CUDA_OK(cudaMemcpyAsync(h->st_text, utf8, bytes, cudaMemcpyHostToDevice, h->stream));
   B2_CUDA_OK(cudaMemcpyAsync(h->st_off, offsets, (n + 1) * 8, cudaMemcpyHostToDevice, h->stream));
   *n_bytes = bytes;
+  return B2_OK;
+}
+
+// b2_tokenize for large jobs. In one piece, the upload of the text (0.5 GB for a million lines), the
+// kernel and the read-back of ids and masks (0.64 GB) take about 20 ms each and run back to back, which
+// makes the end-to-end rate half the kernel's. Here the job is cut into chunks of TOKENIZE_PIPE_CHUNK
+// lines that go round three side streams, each chunk uploading its own byte range, running the kernel
+// on its lines and sending its rows back: chunk k's results travel to the host while chunk k+1 is
+// tokenised and chunk k+2's text arrives (the two copy directions have their own engines). The kernel
+// reads lines at their absolute offsets, so every chunk lands where a one-shot copy would have put it
+// and its output rows are the rows of the whole job: results are bit-identical to the one-shot path.
+// The offsets (needed by every chunk) are already on their way on the handle's stream; the caller holds
+// the handle's lock. Host buffers should be pinned for the copies to overlap (pageable ones still work).
+constexpr int64_t TOKENIZE_PIPE_CHUNK = 65536;
+
+static int tokenize_pipelined(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n, int64_t bytes,
+                              int32_t max_len, int32_t* ids, uint8_t* mask, int32_t* d_ids, uint8_t* d_mask,
+                              b2_metrics* out) {
+  constexpr int S = 3;
+  for (int l = 0; l < S; ++l) {
+    if (!h->copy_stream[l]) B2_CUDA_OK(cudaStreamCreateWithFlags(&h->copy_stream[l], cudaStreamNonBlocking));
+    if (!h->pin_ev[l][0]) B2_CUDA_OK(cudaEventCreateWithFlags(&h->pin_ev[l][0], cudaEventDisableTiming));
+  }
+  cudaStream_t st = h->stream;
+  B2_CUDA_OK(cudaEventRecord(h->ev_begin, st));
+  B2_CUDA_OK(cudaEventRecord(h->ev_run, st));  // behind the upload of the offsets
+  int rc = B2_OK;
+  int64_t launches = 0;
+  for (int64_t a = 0, c = 0; a < n; a += TOKENIZE_PIPE_CHUNK, ++c) {
+    const int64_t cnt = std::min<int64_t>(TOKENIZE_PIPE_CHUNK, n - a);
+    const int64_t lo = offsets[a], hi = offsets[a + cnt];
+    if (lo < 0 || hi < lo || hi > bytes) {
+      set_last_error("text input: offsets[%lld..%lld] are not non-decreasing within [0, %lld]",
+                     static_cast<long long>(a), static_cast<long long>(a + cnt), static_cast<long long>(bytes));
+      rc = B2_ERR_ARG;
+      break;
+    }
+    cudaStream_t s = h->copy_stream[c % S];
+    if (c < S) B2_CUDA_OK(cudaStreamWaitEvent(s, h->ev_run, 0));
+    if (hi > lo) B2_CUDA_OK(cudaMemcpyAsync(h->st_text + lo, utf8 + lo, size_t(hi - lo), cudaMemcpyHostToDevice, s));
+    if ((rc = tokenizer_run(s, h->tok, h->st_text, h->st_off + a, static_cast<int>(cnt), max_len,
+                            d_ids + a * max_len, d_mask ? d_mask + a * max_len : nullptr, nullptr, h->num_sms)))
+      break;
+    ++launches;
+    B2_CUDA_OK(cudaMemcpyAsync(ids + a * max_len, d_ids + a * max_len, size_t(cnt) * max_len * 4,
+                               cudaMemcpyDeviceToHost, s));
+    if (mask)
+      B2_CUDA_OK(cudaMemcpyAsync(mask + a * max_len, d_mask + a * max_len, size_t(cnt) * max_len,
+                                 cudaMemcpyDeviceToHost, s));
+  }
+  for (int l = 0; l < S; ++l) {   // the handle's stream waits for the side streams, also on the error path
+    B2_CUDA_OK(cudaEventRecord(h->pin_ev[l][0], h->copy_stream[l]));
+    B2_CUDA_OK(cudaStreamWaitEvent(st, h->pin_ev[l][0], 0));
+  }
+  B2_CUDA_OK(cudaEventRecord(h->ev_end, st));
+  B2_CUDA_OK(cudaStreamSynchronize(st));
+  if (rc) return rc;
+  B2_CUDA_OK(cudaGetLastError());
+  float ms = 0.f;
+  B2_CUDA_OK(cudaEventElapsedTime(&ms, h->ev_begin, h->ev_end));
+  KindAcc acc;
+  acc.launches = launches;
+  fill_metrics(out, h, acc, n, 0, n * max_len, 1, 0, 0, ms);
   return B2_OK;
 }
 
@@ -1095,13 +1159,19 @@ int b2_tokenize(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64
   if (!h) { set_last_error("b2_tokenize: NULL handle"); return B2_ERR_ARG; }
   int64_t bytes = 0;
   size_t out_ids = 0, out_mask = 0;
+  bool pipelined = false;
   {
     std::lock_guard<std::mutex> lock(h->mu);
     DeviceGuard guard(h->device);
     if (max_len < 2) { set_last_error("tokenize: max_len must be >= 2"); return B2_ERR_ARG; }
+    if (!h->has_tokenizer) {
+      set_last_error("this handle was created without a tokenizer (b2_config.vocab_path was NULL)");
+      return B2_ERR_ARG;
+    }
     if (n > 0 && !ids) { set_last_error("tokenize: ids is NULL"); return B2_ERR_ARG; }
     int rc;
-    if ((rc = stage_text(h, utf8, offsets, n, &bytes))) return rc;
+    pipelined = n >= 2 * TOKENIZE_PIPE_CHUNK && !h->profiling;
+    if ((rc = stage_text(h, utf8, offsets, n, &bytes, !pipelined))) return rc;
     out_ids = size_t(n) * max_len * 4;
     out_mask = mask ? size_t(n) * max_len : 0;
     if ((rc = grow(&h->st_out, &h->st_out_cap, out_ids + out_mask + 64))) return rc;
@@ -1111,6 +1181,21 @@ int b2_tokenize(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64
   b2_metrics local;
   memset(&local, 0, sizeof(local));
   local.struct_size = sizeof(local);
+  if (pipelined) {
+    // large jobs: upload, kernel and download of successive chunks overlap on three streams
+    std::lock_guard<std::mutex> lock(h->mu);
+    DeviceGuard guard(h->device);
+    int rc = tokenize_pipelined(h, utf8, offsets, n, bytes, max_len, ids, mask, d_ids, d_mask, &local);
+    if (rc) return rc;
+    local.h2d_bytes = bytes + (n + 1) * 8;
+    local.d2h_bytes = out_ids + out_mask;
+    if (metrics && metrics->struct_size > 0) {
+      const int32_t keep = metrics->struct_size;
+      memcpy(metrics, &local, std::min<size_t>(sizeof(local), keep));
+      metrics->struct_size = keep;
+    }
+    return B2_OK;
+  }
   int rc = b2_tokenize_device(h, h->st_text, h->st_off, n, bytes, max_len, d_ids, d_mask, &local);
   if (rc) return rc;
   {
