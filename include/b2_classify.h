@@ -109,7 +109,9 @@ uint64_t b2_get_stream(b2_handle* h);
 /* WordPiece tokenize-and-pad. utf8 holds the n items back to back, item i is bytes
  * [offsets[i], offsets[i+1]). ids: [n, max_len] int32, mask: [n, max_len] uint8 (either may be
  * NULL). No reference counterpart; shared by map_tokenize (mode "wordpiece") and
- * map_classify_tpu. Host pointers. */
+ * map_classify_tpu. Host pointers. Jobs of 131,072 items or more run as 65,536-item chunks on three
+ * streams, so that the upload of one chunk, the kernel of the next and the read-back of a third
+ * overlap (same results); page-locked host buffers are what lets the copies overlap. */
 int b2_tokenize(b2_handle* h, const uint8_t* utf8, const int64_t* offsets, int64_t n, int32_t max_len,
                 int32_t* ids, uint8_t* mask, b2_metrics* metrics);
 /* Same with every pointer in device memory on the handle's device (inputs already resident). */
