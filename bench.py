@@ -1046,6 +1046,10 @@ def main():
                                    f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
                                    "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:])
     claim_stdout()
+    if args.impl == "reference":
+        # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is to use all the host threads it
+        # can (torch is imported only further down, so dropping the variable here is early enough)
+        os.environ.pop("OMP_NUM_THREADS", None)
     if wl["kind"] == "loop":
         run_agent_loop(args, args.workload, wl, rank, args.impl == "reference")
         return
